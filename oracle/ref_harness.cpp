@@ -1,0 +1,175 @@
+// TEST INFRASTRUCTURE ONLY -- never linked into the product.
+//
+// Thin driver around the UNMODIFIED reference headers (compiled from where they
+// lie under /root/reference, see oracle/Makefile; output goes to oracle/_ref/).
+// It reads hot-path cases from a line-based text file and prints what the
+// reference computes, so the C restatement (oracle/sviper_oracle.c) and the CUDA
+// path can be pinned against the real SeqAn/SViper code.
+//
+// Commands (one per line, whitespace separated; '*' = empty string):
+//   ALIGNX  mm mx ge go  ref read          generic semi-global affine (SeqAn golden vectors)
+//   ALIGN   ref read qual                  sviper::map_single_read      (mapping.h:84-137)
+//   ROUND   fix ins_mean ins_sd n ref  then n lines "r1 q1 r2 q2"   one polish() round with profile dump
+//   POLISH  ins_mean ins_sd n ref      then n lines "r1 q1 r2 q2"   polish_to_perfection (polishing.h:319)
+//   FINAL   ref_part polished              convex-gap global alignment + CIGAR (sviper.h:452-466)
+#include <thread>
+#include <omp.h>
+#include <cstdio>
+#include <cstring>
+#include <iostream>
+#include <fstream>
+#include <sstream>
+#include <string>
+#include <vector>
+
+#include <seqan/align.h>
+#include <seqan/bam_io.h>
+#include <sviper/config.h>
+#include <sviper/polishing.h>
+
+using namespace seqan;
+
+static std::string hexd(double d)
+{
+    char buf[64];
+    snprintf(buf, sizeof buf, "%a", d);
+    return buf;
+}
+
+template <typename TGaps>
+static std::string row(TGaps const & g)
+{
+    std::string s;
+    for (unsigned i = 0; i < length(g); ++i)
+        s += isGap(g, i) ? '-' : (char)Dna5(g[i]);
+    return s.empty() ? "*" : s;
+}
+
+static Dna5QString mkread(std::string const & s, std::string const & q)
+{
+    Dna5QString r;
+    if (s == "*") return r;
+    for (size_t i = 0; i < s.size(); ++i)
+    {
+        Dna5Q c = Dna5Q(s[i]);
+        assignQualityValue(c, (int)q[i] - 33);
+        appendValue(r, c);
+    }
+    return r;
+}
+
+static void read_pairs(std::istream & in, unsigned n, StringSet<Dna5QString> & r1, StringSet<Dna5QString> & r2)
+{
+    for (unsigned i = 0; i < n; ++i)
+    {
+        std::string a, qa, b, qb;
+        in >> a >> qa >> b >> qb;
+        appendValue(r1, mkread(a, qa));
+        appendValue(r2, mkread(b, qb));
+    }
+}
+
+static std::string dna(Dna5String const & s)
+{
+    std::string o;
+    for (unsigned i = 0; i < length(s); ++i) o += (char)s[i];
+    return o.empty() ? "*" : o;
+}
+
+int main(int argc, char ** argv)
+{
+    if (argc < 2) { std::cerr << "usage: ref_harness cases.txt\n"; return 2; }
+    std::ifstream in(argv[1]);
+    std::string cmd;
+    while (in >> cmd)
+    {
+        if (cmd == "ALIGNX")
+        {
+            int mm, mx, ge, go; std::string ref, rd;
+            in >> mm >> mx >> ge >> go >> ref >> rd;
+            Dna5String h = ref; Dna5String v = rd;
+            Gaps<Dna5String, ArrayGaps> gh(h), gv(v);
+            int s = globalAlignment(gh, gv, Score<int, Simple>(mm, mx, ge, go),
+                                    AlignConfig<true, false, false, true>(), AffineGaps());
+            std::cout << "ALIGNX score=" << s << " ref=" << row(gh) << " read=" << row(gv) << "\n";
+        }
+        else if (cmd == "ALIGN")
+        {
+            std::string ref, rd, q;
+            in >> ref >> rd >> q;
+            Dna5String h = ref; Dna5QString r = mkread(rd, q);
+            Gaps<Dna5QString, ArrayGaps> gr; Gaps<Dna5String, ArrayGaps> gh;
+            assignSource(gr, r); assignSource(gh, h);
+            double mapQ = 0;
+            bool rc = sviper::map_single_read(gr, gh, r, h, mapQ);
+            std::cout << "ALIGN rc=" << rc << " mapQ=" << (int)mapQ
+                      << " lead=" << sviper::gapsBeginPos(gr) << " end=" << sviper::gapsEndPos(gr)
+                      << " ref=" << row(gh) << " read=" << row(gr) << "\n";
+        }
+        else if (cmd == "ROUND" || cmd == "POLISH")
+        {
+            int fix = 0; double im, isd; unsigned n; std::string ref;
+            if (cmd == "ROUND") in >> fix;
+            in >> im >> isd >> n >> ref;
+            StringSet<Dna5QString> r1, r2;
+            read_pairs(in, n, r1, r2);
+            sviper::CmdOptions opt;
+            opt.mean_insert_size_of_short_reads = im;
+            opt.stdev_insert_size_of_short_reads = isd;
+            sviper::SViperConfig config{opt};
+            config.ref_flank_length = 500;
+            sviper::compute_baseQ_stats(config, r1, r2);
+            Dna5String h = ref;
+            if (cmd == "POLISH")
+            {
+                Dna5String out = sviper::polish_to_perfection(r1, r2, h, config);
+                std::cout << "POLISH rounds=" << config.rounds << " subst=" << config.substituted_bases
+                          << " ins=" << config.inserted_bases << " del=" << config.deleted_bases
+                          << " baseQ_mean=" << hexd(config.baseQ_mean) << " mappQ_mean=" << hexd(config.mappQ_mean)
+                          << " seq=" << dna(out) << " cov=";
+                for (size_t i = 0; i < config.cov_profile.size(); ++i) std::cout << (i ? "," : "") << config.cov_profile[i];
+                std::cout << "\n";
+            }
+            else
+            {
+                // body of sviper::polish (polishing.h:295-317) with the profile exposed
+                config.fix_indels = fix;
+                Gaps<Dna5String, ArrayGaps> contigGaps(h);
+                std::vector<sviper::Mapping_object> mobs = sviper::mapping(r1, r2, h, config);
+                sviper::compute_mappQ_stats(config, mobs);
+                String<ProfileChar<Dna5, double> > profile;
+                resize(profile, length(h));
+                config.cov_profile.clear();
+                resize(config.cov_profile, length(h));
+                sviper::fill_profile(profile, config.cov_profile, contigGaps, mobs, config);
+                Dna5String out = sviper::consensus_from_profile(profile, contigGaps, config);
+                std::cout << "ROUND subst=" << config.substituted_bases << " ins=" << config.inserted_bases
+                          << " del=" << config.deleted_bases << " baseQ_mean=" << hexd(config.baseQ_mean)
+                          << " mappQ_mean=" << hexd(config.mappQ_mean) << " seq=" << dna(out) << " proper=";
+                for (size_t i = 0; i < mobs.size(); ++i) std::cout << (mobs[i].proper_pair ? '1' : '0');
+                std::cout << " gaps=" << row(contigGaps) << " cov=";
+                for (size_t i = 0; i < config.cov_profile.size(); ++i) std::cout << (i ? "," : "") << config.cov_profile[i];
+                std::cout << " profile=";
+                for (unsigned i = 0; i < length(profile); ++i)
+                    for (int k = 0; k < 6; ++k) std::cout << ((i || k) ? "," : "") << hexd(profile[i].count[k]);
+                std::cout << "\n";
+            }
+        }
+        else if (cmd == "FINAL")
+        {
+            std::string a, b; in >> a >> b;
+            Dna5String ref_part = a, polished = b;
+            sviper::CmdOptions opt; sviper::SViperConfig config{opt};
+            Gaps<Dna5String, ArrayGaps> gapsRef(ref_part), gapsSeq(polished);
+            double s = globalAlignment(gapsRef, gapsSeq, Score<double, Simple>(config.MM, config.MX, config.GE, config.GO),
+                                       AlignConfig<false, false, false, false>(), ConvexGaps());
+            String<CigarElement<char, unsigned> > cigar;
+            getCigarString(cigar, gapsRef, gapsSeq, std::numeric_limits<unsigned>::max());
+            std::cout << "FINAL score=" << hexd(s) << " ncigar=" << length(cigar) << " cigar=";
+            for (unsigned i = 0; i < length(cigar); ++i) std::cout << cigar[i].count << cigar[i].operation;
+            std::cout << "\n";
+        }
+        else { std::cerr << "unknown command " << cmd << "\n"; return 2; }
+    }
+    return 0;
+}
