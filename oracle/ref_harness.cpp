@@ -9,8 +9,8 @@
 // Commands (one per line, whitespace separated; '*' = empty string):
 //   ALIGNX  mm mx ge go  ref read          generic semi-global affine (SeqAn golden vectors)
 //   ALIGN   ref read qual                  sviper::map_single_read      (mapping.h:84-137)
-//   ROUND   fix ins_mean ins_sd n ref  then n lines "r1 q1 r2 q2"   one polish() round with profile dump
-//   POLISH  ins_mean ins_sd n ref      then n lines "r1 q1 r2 q2"   polish_to_perfection (polishing.h:319)
+//   ROUND   fix flank ins_mean ins_sd n ref  then n lines "r1 q1 r2 q2"   one polish() round with profile dump
+//   POLISH  flank ins_mean ins_sd n ref      then n lines "r1 q1 r2 q2"   polish_to_perfection (polishing.h:319)
 //   FINAL   ref_part polished              convex-gap global alignment + CIGAR (sviper.h:452-466)
 #include <thread>
 #include <omp.h>
@@ -108,16 +108,16 @@ int main(int argc, char ** argv)
         }
         else if (cmd == "ROUND" || cmd == "POLISH")
         {
-            int fix = 0; double im, isd; unsigned n; std::string ref;
+            int fix = 0; unsigned flank; double im, isd; unsigned n; std::string ref;
             if (cmd == "ROUND") in >> fix;
-            in >> im >> isd >> n >> ref;
+            in >> flank >> im >> isd >> n >> ref;
             StringSet<Dna5QString> r1, r2;
             read_pairs(in, n, r1, r2);
             sviper::CmdOptions opt;
             opt.mean_insert_size_of_short_reads = im;
             opt.stdev_insert_size_of_short_reads = isd;
             sviper::SViperConfig config{opt};
-            config.ref_flank_length = 500;
+            config.ref_flank_length = flank;
             sviper::compute_baseQ_stats(config, r1, r2);
             Dna5String h = ref;
             if (cmd == "POLISH")
