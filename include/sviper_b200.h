@@ -1,0 +1,178 @@
+/* sviper_b200 -- C ABI of the B200 (sm_100a) implementation of SViper's per-variant polishing hot path.
+ *
+ * The reference (smehringer/SViper) has no plugin/FFI interface: the hot path is three call seams inside
+ * one translation unit. Each entry point below replaces one of them:
+ *
+ *   svp_polish_batch        include/sviper/polishing.h:319-346  polish_to_perfection(reads1, reads2, ref, config),
+ *                           called at include/sviper/sviper.h:431, plus (when ref_part is given) the final
+ *                           alignment + CIGAR at include/sviper/sviper.h:452-466
+ *   svp_final_align_batch   include/sviper/sviper.h:457-466     globalAlignment(..., ConvexGaps()) + getCigarString
+ *   svp_align_batch         include/sviper/mapping.h:84-137     map_single_read (fwd + RC semi-global affine
+ *                           alignment, strand pick, mapQ) -- also the config-5 GCUPS microbenchmark entry
+ *   svp_submit_* / svp_wait_any   src/sviper.cpp:43-47          the per-variant OpenMP loop -> device batch scheduler
+ *
+ * Conventions: plain C types; all pointers are HOST memory owned by the caller; device memory is owned by
+ * the context; bases are uint8 0..4 = A,C,G,T,N (seqan::Dna5 ordValue); qualities uint8 0..62 with N carrying
+ * 0 (seqan::Dna5Q, extern/seqan/include/seqan/basic/alphabet_residue.h:331-365). Every function returns
+ * SVP_OK (0) or a negative error; any CUDA error is fatal for the call -- there is NO CPU fallback.
+ * One context per GPU; a context is used by one thread at a time.
+ */
+#ifndef SVIPER_B200_H
+#define SVIPER_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SVP_OK 0
+#define SVP_ERR_CUDA (-1)        /* a CUDA call or kernel failed; svp_last_error() has the text */
+#define SVP_ERR_ARG (-2)         /* invalid argument (empty read1, window shorter than 2*flank, ...) */
+#define SVP_ERR_CAPACITY (-3)    /* a window outgrew its buffers (consensus grew beyond 2x + 4096) */
+#define SVP_ERR_UNSUPPORTED (-4) /* read longer than SVP_MAX_READ_LEN */
+
+#define SVP_MAX_READ_LEN 256
+
+typedef struct svp_ctx svp_ctx;
+
+/* Creates a context on cuda_device. cuda_stream: a cudaStream_t (as void*) every kernel and copy of this
+ * context is issued on; NULL = the context creates its own stream. */
+svp_ctx *svp_create(int cuda_device, void *cuda_stream);
+void svp_destroy(svp_ctx *ctx);
+const char *svp_last_error(const svp_ctx *ctx);
+const char *svp_version(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * map_single_read batch (include/sviper/mapping.h:84-137).
+ * Task t aligns read read_id[t] against window win_id[t], forward and reverse-complement, full
+ * unbanded semi-global DP, Score<int>(1,-4,-1,-6) (mapping.h:94-97).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct
+{
+    int32_t n_reads;
+    const uint8_t *read_bases;   /* concatenated */
+    const int32_t *read_off;     /* n_reads + 1 offsets into read_bases */
+    int32_t n_windows;
+    const uint8_t *win_bases;    /* concatenated */
+    const int32_t *win_off;      /* n_windows + 1 */
+    int32_t n_tasks;
+    const int32_t *task_read;    /* n_tasks */
+    const int32_t *task_win;     /* n_tasks */
+} svp_align_in;
+
+typedef struct
+{
+    /* each n_tasks long; any pointer may be NULL to skip that output */
+    int32_t *score;      /* forward-strand score */
+    int32_t *score_rc;   /* reverse-complement score */
+    int32_t *is_rc;      /* 1 iff !(score > score_rc)           (mapping.h:121) */
+    int32_t *lead;       /* gapsBeginPos(gapsRead) of the winner (mapping.h:66-70) */
+    int32_t *endpos;     /* gapsEndPos(gapsRead) of the winner   (mapping.h:59-63) */
+    /* optional alignment of the winner, one op per view column between the read row's leading and
+     * trailing gaps: 'M' base/base, 'D' gap in read row, 'I' gap in consensus row. ops_cap bytes per
+     * task; ops_len[t] = number of ops (ops beyond ops_cap are dropped). May be NULL. */
+    char *ops;
+    int32_t ops_cap;
+    int32_t *ops_len;
+} svp_align_out;
+
+/* with_traceback = 0: scores / strand only (lead, endpos, ops are not written). */
+int svp_align_batch(svp_ctx *ctx, const svp_align_in *in, svp_align_out *out, int with_traceback);
+
+/* Same work as svp_align_batch(with_traceback=0) but inputs already resident on the device from the last
+ * svp_align_batch call: re-runs the kernels only (used by bench.py for the HBM-resident `value`).
+ * kernel_ms (may be NULL) receives the CUDA-event time of the dominant (score) kernel alone. */
+int svp_align_rerun(svp_ctx *ctx, int with_traceback, float *kernel_ms);
+
+/* ------------------------------------------------------------------------------------------------
+ * polish_to_perfection (+ final alignment) for a batch of independent variants.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct
+{
+    /* flanked consensus (include/sviper/sviper.h:419-422) */
+    const uint8_t *consensus;
+    int32_t consensus_len;
+    int32_t ref_flank_length;           /* SViperConfig::ref_flank_length, 500 (sviper.h:363) */
+    /* read pairs: reads2[i] is the mate of reads1[i]; a zero-length mate is the dummy (basics.h:317,398) */
+    int32_t n_pairs;
+    const uint8_t *reads1_bases, *reads1_quals;
+    const int32_t *reads1_off;          /* n_pairs + 1 */
+    const uint8_t *reads2_bases, *reads2_quals;
+    const int32_t *reads2_off;          /* n_pairs + 1 */
+    /* SViperConfig scalars (include/sviper/config.h) */
+    double baseQ_mean;                  /* compute_baseQ_stats, polishing.h:197-234 (host, sviper.h:426) */
+    double insert_mean, insert_sd;      /* CmdOptions, config.h:16-17 */
+    double min_coverage;                /* config.h:79 (4) */
+    /* optional reference part for the final alignment (sviper.h:447-450); NULL = polish only */
+    const uint8_t *ref_part;
+    int32_t ref_part_len;
+} svp_window_in;
+
+typedef struct
+{
+    int32_t status;                     /* SVP_OK or a per-variant error */
+    /* polished sequence (caller buffer of polished_cap bytes) */
+    uint8_t *polished;
+    int32_t polished_cap;
+    int32_t polished_len;
+    /* SViperConfig side effects (config.h:72-90) */
+    uint32_t rounds, substituted_bases, inserted_bases, deleted_bases;
+    double mappQ_mean;
+    /* coverage profile of the last round (config.cov_profile; logged at sviper.h:441-443). Optional. */
+    uint32_t *cov_profile;
+    int32_t cov_cap;
+    int32_t cov_len;
+    /* final alignment CIGAR (sviper.h:466); filled when ref_part was given. Optional buffers. */
+    char *cigar_op;
+    uint32_t *cigar_cnt;
+    int32_t cigar_cap;
+    int32_t n_cigar;                    /* number of CIGAR elements (assign_quality uses only this) */
+    double final_score;
+} svp_result;
+
+int svp_polish_batch(svp_ctx *ctx, int32_t n_variants, const svp_window_in *in, svp_result *out);
+
+/* Final alignment only: ref_part[i] (H) vs seq[i] (V), Score<double>(90000,-80000,-1,-100000), ConvexGaps. */
+typedef struct
+{
+    const uint8_t *ref_part;
+    int32_t ref_part_len;
+    const uint8_t *seq;
+    int32_t seq_len;
+} svp_final_in;
+
+int svp_final_align_batch(svp_ctx *ctx, int32_t n, const svp_final_in *in, svp_result *out);
+
+/* include/sviper/evaluate_final_mapping.h:17-28 (host arithmetic, provided for completeness) */
+double svp_assign_quality(int32_t n_cigar, int32_t flanking_region);
+
+/* ------------------------------------------------------------------------------------------------
+ * Batch scheduler facade (replaces the loop body at src/sviper.cpp:43-47): submissions are queued and
+ * executed as one device batch on the first svp_wait_any after them. The structs (and everything they
+ * point to) must stay valid until their result has been returned.
+ * ---------------------------------------------------------------------------------------------- */
+int svp_submit_polish(svp_ctx *ctx, uint64_t tag, const svp_window_in *w, svp_result *r);
+int svp_wait_any(svp_ctx *ctx, uint64_t *tag, svp_result **r);   /* returns 1 when nothing is pending */
+
+/* ------------------------------------------------------------------------------------------------
+ * Debug / measurement hooks
+ * ---------------------------------------------------------------------------------------------- */
+/* One polishing round (sviper::polish, polishing.h:295-317) on a single window with the profile exposed:
+ * profile = Lp x 6 doubles, cov = Lp, isgap = Lp (1 = inserted column), proper = n_pairs flags. */
+int svp_debug_round(svp_ctx *ctx, const svp_window_in *w, int fix_indels, double *profile, uint32_t *cov,
+                    uint8_t *isgap, int32_t cap_cols, int32_t *n_cols, uint8_t *proper, uint8_t *out_seq,
+                    int32_t out_cap, int32_t *out_len, double *mappQ_mean, uint32_t *counters /* subst, ins, del */);
+
+/* Measures the sustained rate of the DPX-class packed 16x2 instructions the score kernel is made of
+ * (VIADDMNMX / VIMNMX3 / IADD), in lane-operations per second over the whole chip. */
+int svp_probe_dpx(svp_ctx *ctx, double *viaddmax_lane_ops, double *vimax3_lane_ops, double *mix_lane_ops);
+
+/* Per-kernel launch counts and CUDA-event milliseconds accumulated since the last reset.
+ * names: k1_score, k1_trace, k2_traceback, k3_pileup_vote, k5_final, k5_traceback, pack */
+int svp_stats(svp_ctx *ctx, int32_t *n_launches, double *ms_by_kernel /* 8 entries */, int reset);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,269 @@
+"""Python host side over the C ABI (include/sviper_b200.h). SViper itself is C++; this mirror exists so
+that tests and bench.py read like the reference's call sites:
+
+    mapping / map_single_read     include/sviper/mapping.h:84-179      -> Context.align_batch
+    polish_to_perfection          include/sviper/polishing.h:319-346   -> Context.polish_batch
+    final globalAlignment+CIGAR   include/sviper/sviper.h:452-466      -> Context.final_align_batch
+    assign_quality                include/sviper/evaluate_final_mapping.h:17-28 -> assign_quality
+
+Every call goes to the CUDA library; if it is missing or no GPU is present this module raises --
+there is no CPU implementation behind it.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libsviper_b200.so")
+
+u8p, i32p, u32p, f64p = (C.POINTER(t) for t in (C.c_uint8, C.c_int32, C.c_uint32, C.c_double))
+
+
+class AlignIn(C.Structure):
+    _fields_ = [("n_reads", C.c_int32), ("read_bases", u8p), ("read_off", i32p), ("n_windows", C.c_int32),
+                ("win_bases", u8p), ("win_off", i32p), ("n_tasks", C.c_int32), ("task_read", i32p),
+                ("task_win", i32p)]
+
+
+class AlignOut(C.Structure):
+    _fields_ = [("score", i32p), ("score_rc", i32p), ("is_rc", i32p), ("lead", i32p), ("endpos", i32p),
+                ("ops", C.c_char_p), ("ops_cap", C.c_int32), ("ops_len", i32p)]
+
+
+class WindowIn(C.Structure):
+    _fields_ = [("consensus", u8p), ("consensus_len", C.c_int32), ("ref_flank_length", C.c_int32),
+                ("n_pairs", C.c_int32), ("reads1_bases", u8p), ("reads1_quals", u8p), ("reads1_off", i32p),
+                ("reads2_bases", u8p), ("reads2_quals", u8p), ("reads2_off", i32p), ("baseQ_mean", C.c_double),
+                ("insert_mean", C.c_double), ("insert_sd", C.c_double), ("min_coverage", C.c_double),
+                ("ref_part", u8p), ("ref_part_len", C.c_int32)]
+
+
+class Result(C.Structure):
+    _fields_ = [("status", C.c_int32), ("polished", u8p), ("polished_cap", C.c_int32), ("polished_len", C.c_int32),
+                ("rounds", C.c_uint32), ("substituted_bases", C.c_uint32), ("inserted_bases", C.c_uint32),
+                ("deleted_bases", C.c_uint32), ("mappQ_mean", C.c_double), ("cov_profile", u32p),
+                ("cov_cap", C.c_int32), ("cov_len", C.c_int32), ("cigar_op", C.c_char_p), ("cigar_cnt", u32p),
+                ("cigar_cap", C.c_int32), ("n_cigar", C.c_int32), ("final_score", C.c_double)]
+
+
+class FinalIn(C.Structure):
+    _fields_ = [("ref_part", u8p), ("ref_part_len", C.c_int32), ("seq", u8p), ("seq_len", C.c_int32)]
+
+
+EXPORTS = ["svp_create", "svp_destroy", "svp_last_error", "svp_version", "svp_align_batch", "svp_align_rerun",
+           "svp_polish_batch", "svp_final_align_batch", "svp_assign_quality", "svp_submit_polish", "svp_wait_any",
+           "svp_debug_round", "svp_probe_dpx", "svp_stats"]
+
+_lib = None
+
+
+def build():
+    subprocess.check_call(["make", "-s", "-C", os.path.join(_HERE, "csrc"), "libsviper_b200.so"])
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError("sviper_b200: %s is missing -- run __graft_entry__.build(); there is no CPU fallback"
+                               % LIB_PATH)
+        L = C.CDLL(LIB_PATH)
+        L.svp_create.restype = C.c_void_p
+        L.svp_create.argtypes = [C.c_int, C.c_void_p]
+        L.svp_destroy.argtypes = [C.c_void_p]
+        L.svp_last_error.restype = C.c_char_p
+        L.svp_last_error.argtypes = [C.c_void_p]
+        L.svp_version.restype = C.c_char_p
+        L.svp_align_batch.argtypes = [C.c_void_p, C.POINTER(AlignIn), C.POINTER(AlignOut), C.c_int]
+        L.svp_align_rerun.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_float)]
+        L.svp_polish_batch.argtypes = [C.c_void_p, C.c_int32, C.POINTER(WindowIn), C.POINTER(Result)]
+        L.svp_final_align_batch.argtypes = [C.c_void_p, C.c_int32, C.POINTER(FinalIn), C.POINTER(Result)]
+        L.svp_assign_quality.restype = C.c_double
+        L.svp_assign_quality.argtypes = [C.c_int32, C.c_int32]
+        L.svp_submit_polish.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(WindowIn), C.POINTER(Result)]
+        L.svp_wait_any.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.POINTER(Result))]
+        L.svp_debug_round.argtypes = [C.c_void_p, C.POINTER(WindowIn), C.c_int, f64p, u32p, u8p, C.c_int32, i32p, u8p,
+                                      u8p, C.c_int32, i32p, f64p, u32p]
+        L.svp_probe_dpx.argtypes = [C.c_void_p, f64p, f64p, f64p]
+        L.svp_stats.argtypes = [C.c_void_p, i32p, f64p, C.c_int]
+        _lib = L
+    return _lib
+
+
+def _p(a, t=u8p):
+    return a.ctypes.data_as(t)
+
+
+def pack(seqs):
+    """list of uint8 arrays -> (concatenated, int32 offsets)"""
+    off = np.zeros(len(seqs) + 1, np.int32)
+    if len(seqs):
+        off[1:] = np.cumsum([len(s) for s in seqs])
+    cat = np.concatenate([np.asarray(s, np.uint8) for s in seqs] + [np.zeros(0, np.uint8)])
+    return np.ascontiguousarray(cat), off
+
+
+def baseq_mean(quals1, quals2):
+    """compute_baseQ_stats (polishing.h:197-234): host-side scalar prep, done by the caller at sviper.h:426.
+    Note the reference divides by n*len(reads1[0]) + n*len(reads2[0])."""
+    if not len(quals1):
+        return 0.0
+    # integer sums are exact in double, so any summation order equals the reference's sequential loop
+    avg = float(sum(int(np.sum(q, dtype=np.int64)) for q in quals1) + sum(int(np.sum(q, dtype=np.int64)) for q in quals2))
+    den = len(quals1) * len(quals1[0]) + len(quals2) * len(quals2[0])
+    return avg / den if den else float("nan")
+
+
+def assign_quality(n_cigar, flanking_region):
+    return lib().svp_assign_quality(n_cigar, flanking_region)
+
+
+STAT_NAMES = ["k1_score", "k1_trace", "k2_traceback", "k3_pileup_vote", "k5_final", "k5_traceback", "pack", "other"]
+
+
+class Context:
+    def __init__(self, device=0, stream=None):
+        self.L = lib()
+        self.h = self.L.svp_create(device, stream)
+        if not self.h:
+            raise RuntimeError("sviper_b200: cannot create a context on CUDA device %d (no GPU?) -- no CPU fallback"
+                               % device)
+        self._keep = None
+
+    def close(self):
+        if self.h:
+            self.L.svp_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc, what):
+        if rc != 0:
+            raise RuntimeError("%s failed (%d): %s" % (what, rc, self.L.svp_last_error(self.h).decode()))
+
+    # ---- map_single_read ---------------------------------------------------------------------
+    def align_batch(self, reads, windows, task_read, task_win, traceback=True, ops_cap=0):
+        rb, roff = pack(reads)
+        wb, woff = pack(windows)
+        tr = np.ascontiguousarray(task_read, np.int32); tw = np.ascontiguousarray(task_win, np.int32)
+        n = len(tr)
+        ain = AlignIn(len(reads), _p(rb), _p(roff, i32p), len(windows), _p(wb), _p(woff, i32p), n, _p(tr, i32p),
+                      _p(tw, i32p))
+        o = {k: np.zeros(n, np.int32) for k in ("score", "score_rc", "is_rc", "lead", "endpos", "ops_len")}
+        opsbuf = C.create_string_buffer(max(1, n * ops_cap)) if ops_cap else None
+        aout = AlignOut(_p(o["score"], i32p), _p(o["score_rc"], i32p), _p(o["is_rc"], i32p), _p(o["lead"], i32p),
+                        _p(o["endpos"], i32p), C.cast(opsbuf, C.c_char_p) if opsbuf else None, ops_cap,
+                        _p(o["ops_len"], i32p))
+        self._keep = (rb, roff, wb, woff, tr, tw)
+        self._check(self.L.svp_align_batch(self.h, C.byref(ain), C.byref(aout), 1 if traceback else 0), "svp_align_batch")
+        if opsbuf is not None:
+            raw = opsbuf.raw
+            o["ops"] = [raw[t * ops_cap:t * ops_cap + min(ops_cap, int(o["ops_len"][t]))].decode() for t in range(n)]
+        return o
+
+    def align_rerun(self, traceback=False):
+        ms = C.c_float(0)
+        self._check(self.L.svp_align_rerun(self.h, 1 if traceback else 0, C.byref(ms)), "svp_align_rerun")
+        return ms.value
+
+    # ---- polish_to_perfection (+ final alignment) ------------------------------------------------
+    @staticmethod
+    def make_window(v, keep, with_final=True):
+        """v: dict like synth.make_variant / tests.refcases.small_variant"""
+        r1, o1 = pack(v["reads1"]); q1, _ = pack(v["quals1"])
+        r2, o2 = pack(v["reads2"]); q2, _ = pack(v["quals2"])
+        cons = np.ascontiguousarray(v["consensus"], np.uint8)
+        bq = v.get("baseQ_mean")
+        if bq is None:
+            bq = baseq_mean(v["quals1"], v["quals2"])
+        refp = np.ascontiguousarray(v["ref_part"], np.uint8) if (with_final and v.get("ref_part") is not None) else None
+        keep.append((r1, o1, q1, r2, o2, q2, cons, refp))
+        return WindowIn(_p(cons), len(cons), int(v["flank"]), len(v["reads1"]), _p(r1), _p(q1), _p(o1, i32p), _p(r2),
+                        _p(q2), _p(o2, i32p), float(bq), float(v["ins_mean"]), float(v["ins_sd"]),
+                        float(v.get("min_coverage", 4.0)), _p(refp) if refp is not None else None,
+                        len(refp) if refp is not None else 0)
+
+    @staticmethod
+    def make_result(cap, keep, cigar_cap=4096):
+        pol = np.zeros(cap, np.uint8); cov = np.zeros(3 * cap + 1024, np.uint32)
+        cop = C.create_string_buffer(cigar_cap); ccnt = np.zeros(cigar_cap, np.uint32)
+        keep.append((pol, cov, cop, ccnt))
+        r = Result()
+        r.polished = _p(pol); r.polished_cap = cap; r.cov_profile = _p(cov, u32p); r.cov_cap = len(cov)
+        r.cigar_op = C.cast(cop, C.c_char_p); r.cigar_cnt = _p(ccnt, u32p); r.cigar_cap = cigar_cap
+        return r, pol, cov, cop, ccnt
+
+    def polish_batch(self, variants, with_final=True):
+        keep = []
+        n = len(variants)
+        win = (WindowIn * n)(*[self.make_window(v, keep, with_final) for v in variants])
+        res_parts = [self.make_result(len(v["consensus"]) * 2 + 4096, keep) for v in variants]
+        res = (Result * n)(*[p[0] for p in res_parts])
+        self._check(self.L.svp_polish_batch(self.h, n, win, res), "svp_polish_batch")
+        out = []
+        for i in range(n):
+            r = res[i]
+            _, pol, cov, cop, ccnt = res_parts[i]
+            if r.status != 0:
+                raise RuntimeError("variant %d failed with status %d" % (i, r.status))
+            d = dict(polished=pol[:r.polished_len].copy(), rounds=r.rounds, subst=r.substituted_bases,
+                     ins=r.inserted_bases, dele=r.deleted_bases, mappQ_mean=r.mappQ_mean,
+                     cov=cov[:r.cov_len].copy(), n_cigar=r.n_cigar, final_score=r.final_score)
+            if r.n_cigar:
+                d["cigar"] = [(cop.raw[k:k + 1].decode(), int(ccnt[k])) for k in range(r.n_cigar)]
+            out.append(d)
+        return out
+
+    def final_align_batch(self, pairs, cigar_cap=4096):
+        keep = []
+        n = len(pairs)
+        fin = (FinalIn * n)()
+        parts = []
+        for i, (a, b) in enumerate(pairs):
+            a = np.ascontiguousarray(a, np.uint8); b = np.ascontiguousarray(b, np.uint8)
+            keep.append((a, b))
+            fin[i] = FinalIn(_p(a), len(a), _p(b), len(b))
+            parts.append(self.make_result(16, keep, cigar_cap))
+        res = (Result * n)(*[p[0] for p in parts])
+        self._check(self.L.svp_final_align_batch(self.h, n, fin, res), "svp_final_align_batch")
+        out = []
+        for i in range(n):
+            _, _, _, cop, ccnt = parts[i]
+            r = res[i]
+            if r.status != 0:
+                raise RuntimeError("final alignment %d failed with status %d" % (i, r.status))
+            out.append(dict(score=r.final_score, n_cigar=r.n_cigar,
+                            cigar=[(cop.raw[k:k + 1].decode(), int(ccnt[k])) for k in range(r.n_cigar)]))
+        return out
+
+    def debug_round(self, v, fix_indels):
+        keep = []
+        w = self.make_window(v, keep, with_final=False)
+        cap = 4 * len(v["consensus"]) + 4096
+        prof = np.zeros((cap, 6), np.float64); cov = np.zeros(cap, np.uint32); isgap = np.zeros(cap, np.uint8)
+        proper = np.zeros(max(1, len(v["reads1"])), np.uint8); seq = np.zeros(cap, np.uint8)
+        ncols, olen, mq = C.c_int32(), C.c_int32(), C.c_double()
+        cnt = np.zeros(3, np.uint32)
+        self._check(self.L.svp_debug_round(self.h, C.byref(w), fix_indels, _p(prof, f64p), _p(cov, u32p), _p(isgap),
+                                           cap, C.byref(ncols), _p(proper), _p(seq), cap, C.byref(olen), C.byref(mq),
+                                           _p(cnt, u32p)), "svp_debug_round")
+        n = ncols.value
+        return dict(profile=prof[:n].copy(), cov=cov[:n].copy(), isgap=isgap[:n].copy(),
+                    proper=proper[:len(v["reads1"])].copy(), out=seq[:olen.value].copy(), mappQ_mean=mq.value,
+                    subst=int(cnt[0]), ins=int(cnt[1]), dele=int(cnt[2]), baseQ_mean=w.baseQ_mean)
+
+    def probe_dpx(self):
+        a, b, c = C.c_double(), C.c_double(), C.c_double()
+        self._check(self.L.svp_probe_dpx(self.h, C.byref(a), C.byref(b), C.byref(c)), "svp_probe_dpx")
+        return dict(viaddmax=a.value, vimax3=b.value, mix=c.value)
+
+    def stats(self, reset=0):
+        n = C.c_int32(); ms = (C.c_double * 8)()
+        self.L.svp_stats(self.h, C.byref(n), ms, reset)
+        return n.value, dict(zip(STAT_NAMES, list(ms)))

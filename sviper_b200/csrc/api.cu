@@ -1,0 +1,206 @@
+// C ABI of sviper_b200 (see include/sviper_b200.h). Host orchestration only: every base that is aligned,
+// piled up, voted on or traced back is processed by the sm_100a kernels in this directory.
+// There is deliberately no CPU implementation of any of it here (no fallback).
+#include <algorithm>
+#include <cmath>
+#include <cfloat>
+#include <cub/device/device_scan.cuh>
+#include "ctx.cuh"
+#include "k1_score.cuh"
+
+#include "api_align.inc"
+#include "api_polish.inc"
+#include "api_final.inc"
+
+extern "C" {
+
+const char *svp_version(void) { return "sviper_b200 0.1 (sm_100a)"; }
+
+svp_ctx *svp_create(int cuda_device, void *cuda_stream)
+{
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || cuda_device < 0 || cuda_device >= ndev)
+    {
+        fprintf(stderr, "[sviper_b200] no usable CUDA device %d (found %d) -- this library has no CPU path\n",
+                cuda_device, ndev);
+        return nullptr;
+    }
+    if (cudaSetDevice(cuda_device) != cudaSuccess) return nullptr;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, cuda_device) != cudaSuccess) return nullptr;
+    if (prop.major < 10)
+    {
+        fprintf(stderr, "[sviper_b200] device %d is sm_%d%d; this build targets sm_100a only\n", cuda_device,
+                prop.major, prop.minor);
+        return nullptr;
+    }
+    svp_ctx *ctx = new svp_ctx();
+    ctx->device = cuda_device;
+    if (cuda_stream) ctx->stream = (cudaStream_t)cuda_stream;
+    else
+    {
+        if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return nullptr; }
+        ctx->own_stream = true;
+    }
+    cudaEventCreate(&ctx->ev0);
+    cudaEventCreate(&ctx->ev1);
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) ctx->arena_budget = (size_t)(free_b * 0.6);
+    const char *fw = getenv("SVP_FULL_WINDOW");
+    if (fw && fw[0] == '1') ctx->full_window = 1;
+    return ctx;
+}
+
+void svp_destroy(svp_ctx *ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    DevBuf *bufs[] = {&ctx->reads.bytes, &ctx->reads.w2, &ctx->reads.wn, &ctx->reads.off32, &ctx->reads.len,
+                      &ctx->reads.unit_seq, &ctx->reads.byte_off, &ctx->wins.bytes, &ctx->wins.w2, &ctx->wins.wn,
+                      &ctx->wins.off32, &ctx->wins.len, &ctx->wins.unit_seq, &ctx->wins.byte_off, &ctx->read_quals,
+                      &ctx->qual_off, &ctx->task_read, &ctx->task_win, &ctx->task_idx19, &ctx->task_idx32,
+                      &ctx->score_out, &ctx->plans, &ctx->units, &ctx->E, &ctx->scan_tmp, &ctx->trace, &ctx->ops,
+                      &ctx->alns, &ctx->rec_code, &ctx->rec_qual, &ctx->rec_inslen, &ctx->rec_insq, &ctx->descs,
+                      &ctx->states, &ctx->pair_task, &ctx->cons0, &ctx->cons1, &ctx->inslen, &ctx->voff, &ctx->profile,
+                      &ctx->cov, &ctx->isgap, &ctx->decision, &ctx->proper, &ctx->fjobs, &ctx->fref, &ctx->fseq,
+                      &ctx->ftrace, &ctx->fbndS, &ctx->fbndV, &ctx->fbndVL, &ctx->fends, &ctx->fcig_op, &ctx->fcig_cnt,
+                      &ctx->fcig_out, &ctx->gapstep, &ctx->edge};
+    for (DevBuf *b : bufs) b->release();
+    cudaEventDestroy(ctx->ev0);
+    cudaEventDestroy(ctx->ev1);
+    if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char *svp_last_error(const svp_ctx *ctx) { return ctx ? ctx->err.c_str() : "no context"; }
+
+int svp_align_batch(svp_ctx *ctx, const svp_align_in *in, svp_align_out *out, int with_traceback)
+{
+    if (!ctx || !in || !out) return SVP_ERR_ARG;
+    CK(cudaSetDevice(ctx->device));
+    std::vector<int64_t> roff(in->n_reads + 1), woff(in->n_windows + 1);
+    std::vector<int32_t> rlen(in->n_reads);
+    for (int i = 0; i <= in->n_reads; ++i) roff[i] = in->read_off[i];
+    for (int i = 0; i <= in->n_windows; ++i) woff[i] = in->win_off[i];
+    for (int i = 0; i < in->n_reads; ++i) rlen[i] = in->read_off[i + 1] - in->read_off[i];
+    for (int t = 0; t < in->n_tasks; ++t)
+        if (in->task_read[t] < 0 || in->task_read[t] >= in->n_reads || in->task_win[t] < 0 ||
+            in->task_win[t] >= in->n_windows || in->win_off[in->task_win[t] + 1] - in->win_off[in->task_win[t]] < 1)
+            return svp_fail_msg(ctx, SVP_ERR_ARG, "task refers to a missing read/window");
+    int rc = upload_seqs(ctx, ctx->reads, in->n_reads, in->read_bases, roff.data(), nullptr, true);
+    if (rc) return rc;
+    rc = upload_seqs(ctx, ctx->wins, in->n_windows, in->win_bases, woff.data(), nullptr, true);
+    if (rc) return rc;
+    rc = upload_tasks(ctx, in->n_tasks, in->task_read, in->task_win, rlen.data());
+    if (rc) return rc;
+    rc = run_score_pass(ctx, nullptr);
+    if (rc) return rc;
+    const int n = in->n_tasks;
+    std::vector<svp::ScoreOut> sc(n);
+    if (n) CK(cudaMemcpyAsync(sc.data(), ctx->score_out.p, (size_t)n * sizeof(svp::ScoreOut), cudaMemcpyDeviceToHost, ctx->stream));
+    std::vector<svp::AlnOut> al;
+    std::vector<uint8_t> ops;
+    std::vector<int64_t> E;
+    if (with_traceback && n)
+    {
+        rc = run_trace_pass(ctx, nullptr, false);
+        if (rc) return rc;
+        al.resize(n);
+        CK(cudaMemcpyAsync(al.data(), ctx->alns.p, (size_t)n * sizeof(svp::AlnOut), cudaMemcpyDeviceToHost, ctx->stream));
+        if (out->ops)
+        {
+            E.resize(n + 1);
+            ops.resize((size_t)ctx->E_total + (size_t)n * SVP_MAX_READ_LEN);
+            CK(cudaMemcpyAsync(E.data(), ctx->E.p, (size_t)(n + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+            CK(cudaMemcpyAsync(ops.data(), ctx->ops.p, ops.size(), cudaMemcpyDeviceToHost, ctx->stream));
+        }
+    }
+    CK(cudaStreamSynchronize(ctx->stream));
+    for (int t = 0; t < n; ++t)
+    {
+        if (out->score) out->score[t] = sc[t].score_f;
+        if (out->score_rc) out->score_rc[t] = sc[t].score_r;
+        if (out->is_rc) out->is_rc[t] = !(sc[t].score_f > sc[t].score_r);
+        if (!with_traceback) continue;
+        if (al[t].err) return svp_fail_msg(ctx, SVP_ERR_CUDA, "traceback invariant violated (err " + std::to_string(al[t].err) + ")");
+        if (out->lead) out->lead[t] = al[t].lead;
+        if (out->endpos) out->endpos[t] = al[t].endpos;
+        if (out->ops)
+        {
+            // view columns [lead, endpos): leading 'I's, then the path (stored reversed) without its trailing 'D's
+            const uint8_t *p = ops.data() + E[t] + (int64_t)t * SVP_MAX_READ_LEN;
+            int len = al[t].endpos - al[t].lead, k = 0;
+            char *dst = out->ops + (size_t)t * out->ops_cap;
+            for (int i = 0; i < al[t].lead_i && k < len; ++i, ++k) if (k < out->ops_cap) dst[k] = 'I';
+            for (int i = al[t].npath - 1; i >= 0 && k < len; --i, ++k) if (k < out->ops_cap) dst[k] = (char)p[i];
+            if (out->ops_len) out->ops_len[t] = len;
+        }
+    }
+    return SVP_OK;
+}
+
+int svp_align_rerun(svp_ctx *ctx, int with_traceback, float *kernel_ms)
+{
+    if (!ctx || ctx->ntasks == 0) return SVP_ERR_ARG;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaEventRecord(ctx->ev0, ctx->stream));
+    bool t = ctx->timing; ctx->timing = false;
+    int rc = run_score_pass(ctx, nullptr);
+    ctx->timing = t;
+    if (rc) return rc;
+    CK(cudaEventRecord(ctx->ev1, ctx->stream));
+    if (with_traceback) { rc = run_trace_pass(ctx, nullptr, false); if (rc) return rc; }
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (kernel_ms) CK(cudaEventElapsedTime(kernel_ms, ctx->ev0, ctx->ev1));
+    return SVP_OK;
+}
+
+int svp_probe_dpx(svp_ctx *ctx, double *viaddmax_lane_ops, double *vimax3_lane_ops, double *mix_lane_ops)
+{
+    if (!ctx) return SVP_ERR_ARG;
+    CK(cudaSetDevice(ctx->device));
+    const int blocks = 148 * 8, threads = 256, iters = 4096;
+    DevBuf o; CK(o.ensure((size_t)blocks * threads * 4));
+    double *outs[3] = {viaddmax_lane_ops, vimax3_lane_ops, mix_lane_ops};
+    const double ops_per_iter[3] = {8.0, 8.0, 8.0 * 5.0};
+    for (int mode = 0; mode < 3; ++mode)
+    {
+        float best = 1e30f;
+        for (int rep = 0; rep < 4; ++rep)
+        {
+            CK(cudaEventRecord(ctx->ev0, ctx->stream));
+            if (mode == 0) svp::dpx_probe_kernel<0><<<blocks, threads, 0, ctx->stream>>>(o.as<uint32_t>(), iters);
+            else if (mode == 1) svp::dpx_probe_kernel<1><<<blocks, threads, 0, ctx->stream>>>(o.as<uint32_t>(), iters);
+            else svp::dpx_probe_kernel<2><<<blocks, threads, 0, ctx->stream>>>(o.as<uint32_t>(), iters);
+            CK(cudaGetLastError());
+            CK(cudaEventRecord(ctx->ev1, ctx->stream));
+            CK(cudaEventSynchronize(ctx->ev1));
+            float ms = 0; CK(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+            if (rep > 0 && ms < best) best = ms;
+        }
+        if (outs[mode]) *outs[mode] = (double)blocks * threads * iters * ops_per_iter[mode] / (best * 1e-3);
+    }
+    o.release();
+    return SVP_OK;
+}
+
+int svp_stats(svp_ctx *ctx, int32_t *n_launches, double *ms_by_kernel, int reset)
+{
+    if (!ctx) return SVP_ERR_ARG;
+    if (n_launches) *n_launches = ctx->n_launches;
+    if (ms_by_kernel) for (int i = 0; i < ST_N; ++i) ms_by_kernel[i] = ctx->ms[i];
+    if (reset == 1) { ctx->n_launches = 0; for (int i = 0; i < ST_N; ++i) ctx->ms[i] = 0; }
+    if (reset == 2) ctx->timing = true;    // enable per-kernel CUDA-event timing (synchronises after each kernel)
+    if (reset == 3) ctx->timing = false;
+    return SVP_OK;
+}
+
+double svp_assign_quality(int32_t n_cigar, int32_t flanking_region)
+{
+    double error_rate = ((double)n_cigar - 1.0) / (flanking_region * 2.0);
+    double fuzzyness = (1.0 - error_rate / 0.15) * 100.0;
+    return std::max(fuzzyness, 0.0);
+}
+
+}  // extern "C"

@@ -1,0 +1,171 @@
+// Host-side context, growable device buffers and small utility kernels.
+#pragma once
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+#include "../../include/sviper_b200.h"
+#include "common.cuh"
+#include "k1_trace.cuh"
+#include "k3_pileup.cuh"
+#include "k5_final.cuh"
+
+struct DevBuf
+{
+    void *p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes)
+    {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) { cudaError_t e = cudaFree(p); if (e != cudaSuccess) return e; p = nullptr; cap = 0; }
+        size_t want = bytes + bytes / 4 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e != cudaSuccess) return e;
+        cap = want;
+        return cudaSuccess;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    template <typename T> T *as() const { return (T *)p; }
+};
+
+enum { ST_K1 = 0, ST_K1T, ST_K2, ST_K3, ST_K5, ST_K5TB, ST_PACK, ST_OTHER, ST_N };
+
+// device-resident packed sequences (reads or windows)
+struct DevSeqs
+{
+    DevBuf bytes, w2, wn, off32, len, unit_seq, byte_off;
+    int n = 0;
+    int64_t units = 0;
+    svp::SeqStore store() const
+    {
+        svp::SeqStore s;
+        s.w2 = w2.as<uint32_t>(); s.wn = wn.as<uint32_t>(); s.off32 = off32.as<int32_t>(); s.len = len.as<int32_t>();
+        return s;
+    }
+};
+
+struct svp_ctx
+{
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    std::string err;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    int n_launches = 0;
+    double ms[ST_N] = {0};
+    bool timing = false;
+    size_t arena_budget = (size_t)96 << 30;
+    int full_window = 0;   // debug: trace the whole window instead of the provable sub-window
+
+    // ---- align pipeline state (also reused by the polish pipeline) ----
+    DevSeqs reads, wins;
+    DevBuf read_quals, qual_off;            // qualities (bytes) per read, offsets
+    DevBuf task_read, task_win, task_idx19, task_idx32;
+    int ntasks = 0, n19 = 0, n32 = 0;
+    DevBuf score_out, plans, units, E, scan_tmp, trace, ops, alns;
+    DevBuf rec_code, rec_qual, rec_inslen, rec_insq;
+    int64_t E_total = 0;
+    // ---- polish pipeline ----
+    DevBuf descs, states, pair_task, cons0, cons1, inslen, voff, profile, cov, isgap, decision, proper;
+    // ---- final alignment ----
+    DevBuf fjobs, fref, fseq, ftrace, fbndS, fbndV, fbndVL, fends, fcig_op, fcig_cnt, fcig_out, gapstep, edge;
+    int table_size = 0;
+    // ---- scheduler facade ----
+    std::vector<uint64_t> q_tag;
+    std::vector<const svp_window_in *> q_in;
+    std::vector<svp_result *> q_out;
+    size_t q_done = 0, q_ready = 0;
+};
+
+static int svp_fail(svp_ctx *ctx, cudaError_t e, const char *what, const char *file, int line)
+{
+    char buf[512];
+    snprintf(buf, sizeof buf, "CUDA error %d (%s) at %s:%d in %s", (int)e, cudaGetErrorString(e), file, line, what);
+    if (ctx) ctx->err = buf;
+    fprintf(stderr, "[sviper_b200] %s\n", buf);
+    return SVP_ERR_CUDA;
+}
+
+static int svp_fail_msg(svp_ctx *ctx, int code, const std::string &msg)
+{
+    if (ctx) ctx->err = msg;
+    return code;
+}
+
+namespace svp
+{
+// bytes (0..4) -> 2-bit words + N plane. One thread per 32-base unit.
+// len_override (may be null): current length per sequence (polish rounds change the consensus length).
+__global__ void pack_kernel(const uint8_t *__restrict__ bytes, const int64_t *__restrict__ byte_off,
+                            const int32_t *__restrict__ len, const int32_t *__restrict__ off32,
+                            const int32_t *__restrict__ unit_seq, int64_t nunits, uint32_t *__restrict__ w2,
+                            uint32_t *__restrict__ wn)
+{
+    int64_t u = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (u >= nunits) return;
+    int s = unit_seq[u];
+    int pos0 = (int)(u - off32[s]) * 32;
+    int L = len[s];
+    const uint8_t *b = bytes + byte_off[s];
+    uint32_t lo = 0, hi = 0, nm = 0;
+#pragma unroll 8
+    for (int i = 0; i < 32; ++i)
+    {
+        int p = pos0 + i;
+        uint32_t c = (p < L) ? b[p] : 0u;
+        if (c > 3u) { nm |= 1u << i; c = 0u; }
+        if (i < 16) lo |= c << (2 * i); else hi |= c << (2 * (i - 16));
+    }
+    w2[u * 2] = lo; w2[u * 2 + 1] = hi; wn[u] = nm;
+}
+
+// polish rounds: refresh window lengths / byte offsets from the per-variant state
+__global__ void window_refresh_kernel(const VarDesc *__restrict__ descs, const VarState *__restrict__ states, int nv,
+                                      int32_t *__restrict__ win_len, int64_t *__restrict__ win_byte_off,
+                                      int64_t buf1_delta, uint8_t *__restrict__ win_done)
+{
+    int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= nv) return;
+    win_len[v] = states[v].L;
+    win_byte_off[v] = descs[v].cons_off + (states[v].cur ? buf1_delta : 0);
+    win_done[v] = states[v].done ? 1 : 0;
+}
+
+__global__ void count_active_kernel(const VarState *__restrict__ states, int nv, int32_t *__restrict__ out)
+{
+    int v = blockIdx.x * blockDim.x + threadIdx.x;
+    int a = (v < nv) ? !states[v].done : 0;
+    a = __syncthreads_count(a);
+    if (threadIdx.x == 0 && a) atomicAdd(out, a);
+}
+
+// DPX probe: independent dependent-chains per thread, enough threads to fill the chip
+template <int MODE>
+__global__ void dpx_probe_kernel(uint32_t *out, int iters)
+{
+    uint32_t a[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) a[i] = threadIdx.x * 0x00010001u + i;
+    uint32_t c = blockIdx.x | 0x20002000u;
+    for (int it = 0; it < iters; ++it)
+    {
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+        {
+            if (MODE == 0) a[i] = __viaddmax_s16x2(a[i], 0xFFFFFFFFu, c);
+            else if (MODE == 1) a[i] = __vimax3_s16x2(a[i], c, a[(i + 1) & 7]);
+            else
+            {
+                uint32_t x = a[i] + 0x00020007u;                   // IADD
+                uint32_t hh = __viaddmax_s16x2(a[i], 0xFFFFFFFFu, c);
+                uint32_t vv = __viaddmax_s16x2(c, 0xFFFFFFFFu, a[i]);
+                a[i] = __vimax3_s16x2(x, hh, vv) + 0xFFF9FFFAu;      // VIMNMX3 + IADD
+            }
+        }
+    }
+    uint32_t r = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) r ^= a[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = r;
+}
+}  // namespace svp

@@ -1,0 +1,160 @@
+// K1: batched semi-global affine DP, SCORE PASS (both strands of one read packed as s16x2).
+//
+// Replaces the two seqan::globalAlignment calls of sviper::map_single_read
+// (/root/reference/include/sviper/mapping.h:111-119) as far as score, strand choice (mapping.h:121)
+// and the end cell (leftmost last-row maximum, seqan/align/dp_scout.h:168-180) are concerned.
+// The traceback of the winning strand is redone by the traced pass (k1_trace.cuh).
+//
+// Mapping: 8 lanes (one "group") per (read, window) task, 4 tasks per warp. Lane g owns RPL
+// consecutive read rows and sweeps the window columns as a wavefront: at step t it computes column
+// t-g and hands its bottom row (S+go, V) to lane g+1 with one shuffle pair. The low s16 half carries
+// the forward strand, the high half the reverse complement, so every DPX instruction advances two
+// cells. Rows are aligned to the END of the group: unused rows at the top are "extra row 0s"
+// (substitution score 0 keeps S == 0 there, which is exactly the free-begin row of
+// AlignConfig<true,false,false,true>), so the read's last row is always the last slot of lane 7.
+//
+// Per cell pair: 1 LDS (query profile), IADD (diag+sub), VIADDMNMX (H), VIADDMNMX (V), VIMNMX3 (S),
+// IADD (S+go) -- no trace, no compares. Values are biased by +0x2000 so that both halves stay positive
+// and plain 32-bit adds never carry between halves.
+#pragma once
+#include "common.cuh"
+
+namespace svp
+{
+constexpr int K1_G = 8;                // lanes per task
+constexpr int K1_TASKS_PER_BLOCK = 16; // 128 threads
+constexpr int K1_BIAS = 0x2000;
+
+__host__ __device__ constexpr uint32_t k1_pk(int x) { return (uint32_t)((K1_BIAS + x) & 0xffff) * 0x00010001u; }
+
+template <int RPL>
+struct K1Shape
+{
+    static constexpr int NSLOT = K1_G * RPL;
+    static constexpr int PST = (NSLOT + 31) & ~31;     // words per profile row (one window character)
+    static constexpr int TASK_WORDS = 5 * PST + 8;     // +8: successive groups land on different banks
+    static constexpr int SMEM_BYTES = K1_TASKS_PER_BLOCK * TASK_WORDS * 4;
+};
+
+template <int RPL>
+__global__ void __launch_bounds__(128) k1_score_kernel(const int32_t *__restrict__ task_read,
+                                                       const int32_t *__restrict__ task_win,
+                                                       const int32_t *__restrict__ task_idx, int ntasks,
+                                                       const uint8_t *__restrict__ win_done,
+                                                       SeqStore reads, SeqStore wins, ScoreOut *__restrict__ out)
+{
+    using Sh = K1Shape<RPL>;
+    constexpr int G = K1_G, NSLOT = Sh::NSLOT, PST = Sh::PST;
+    extern __shared__ uint32_t k1_smem[];
+    const int g = threadIdx.x & (G - 1), grp = threadIdx.x >> 3;
+    const int slot = blockIdx.x * K1_TASKS_PER_BLOCK + grp;
+    uint32_t *prof = k1_smem + grp * Sh::TASK_WORDS;   // prof[c][k][g]
+
+    int R = 0, L = 0, runit = 0, wunit = 0, task = -1;
+    if (slot < ntasks)
+    {
+        task = task_idx ? task_idx[slot] : slot;
+        int rid = task_read[task], wid = task_win[task];
+        if (win_done && win_done[wid]) task = -1;       // window already converged: nothing to do
+        else
+        {
+            R = reads.len[rid]; runit = reads.off32[rid];
+            L = wins.len[wid]; wunit = wins.off32[wid];
+        }
+    }
+    const bool live = task >= 0;
+    const int pad = NSLOT - R;   // extra "row 0"s at the top
+
+    constexpr uint32_t GE2 = 0xFFFFFFFFu;           // (-1,-1)
+    constexpr uint32_t GO2 = 0u - 0x00060006u;      // 32-bit add of this subtracts 6 from both halves (no borrow)
+    constexpr uint32_t NEG2 = 0x00010001u;          // "-infinity": biased 1
+    constexpr uint32_t ROW0_SO = k1_pk(GAP_OPEN);   // S == 0 plus gap open
+
+    uint32_t so[RPL], h[RPL];
+    // ---- query profile + initial column (non-free: S[i][0] = go + (i-1)*ge, dp_formula_affine.h:291-325)
+#pragma unroll
+    for (int k = 0; k < RPL; ++k)
+    {
+        int row = g * RPL + k - pad + 1;   // 1-based read row; <= 0 -> pad
+        int rf = -1, rr = -1;
+        if (row >= 1)
+        {
+            rf = seq_base(reads, runit, row - 1);
+            int b = seq_base(reads, runit, R - row);
+            rr = (b < 4) ? 3 - b : 4;
+        }
+#pragma unroll
+        for (int c = 0; c < 5; ++c)
+        {
+            uint32_t sf = (row < 1) ? 6u : ((c == rf) ? 7u : 2u);   // sub - go
+            uint32_t sr = (row < 1) ? 6u : ((c == rr) ? 7u : 2u);
+            prof[c * PST + k * G + g] = sf | (sr << 16);
+        }
+        int s0 = (row >= 1) ? -(5 + row) : 0;
+        so[k] = k1_pk(s0 + GAP_OPEN);
+        h[k] = NEG2;
+    }
+    uint32_t prev_up;   // S[i-1][j-1] + go for this lane's first row
+    {
+        int rowa = g * RPL - pad;   // row above the first slot
+        int sa = (rowa >= 1) ? -(5 + rowa) : 0;
+        prev_up = (g == 0) ? ROW0_SO : k1_pk(sa + GAP_OPEN);
+    }
+    uint32_t out_so = so[RPL - 1], out_v = NEG2;
+    uint32_t best = so[RPL - 1];
+    int colF = 0, colR = 0;
+    uint32_t ww = 0, wn = 0;
+    const uint32_t *w2p = wins.w2 + (size_t)wunit * 2;
+    const uint32_t *wnp = wins.wn + (size_t)wunit;
+
+    const int nsteps = __reduce_max_sync(0xffffffffu, live ? L + G - 1 : 0);
+    for (int t = 0; t < nsteps; ++t)
+    {
+        uint32_t r_so = __shfl_up_sync(0xffffffffu, out_so, 1, G);
+        uint32_t r_v = __shfl_up_sync(0xffffffffu, out_v, 1, G);
+        const int jj = t - g;
+        if (jj >= 0 && jj < L)
+        {
+            if (g == 0) { r_so = ROW0_SO; r_v = NEG2; }
+            if ((jj & 15) == 0)
+            {
+                ww = __ldg(w2p + (jj >> 4));
+                if ((jj & 31) == 0) wn = __ldg(wnp + (jj >> 5));
+            }
+            int c = (ww >> ((jj & 15) * 2)) & 3;
+            if ((wn >> (jj & 31)) & 1) c = 4;
+            const uint32_t *pr = prof + c * PST + g;
+            uint32_t diag = prev_up;
+            prev_up = r_so;
+            uint32_t up_so = r_so, up_v = r_v;
+#pragma unroll
+            for (int k = 0; k < RPL; ++k)
+            {
+                uint32_t inter = diag + pr[k * G];
+                diag = so[k];
+                h[k] = __viaddmax_s16x2(h[k], GE2, so[k]);
+                up_v = __viaddmax_s16x2(up_v, GE2, up_so);
+                uint32_t s = __vimax3_s16x2(inter, h[k], up_v);
+                so[k] = s + GO2;
+                up_so = so[k];
+            }
+            out_so = up_so; out_v = up_v;
+            if (g == G - 1)
+            {
+                // strict improvement only: the leftmost maximum wins (dp_scout.h:173). Halves are biased positive.
+                if ((up_so & 0xffffu) > (best & 0xffffu)) colF = jj + 1;
+                if ((up_so >> 16) > (best >> 16)) colR = jj + 1;
+                best = __vmaxs2(best, up_so);
+            }
+        }
+    }
+    if (g == G - 1 && live)
+    {
+        ScoreOut o;
+        o.score_f = (int)(best & 0xffff) - K1_BIAS - GAP_OPEN;
+        o.score_r = (int)(best >> 16) - K1_BIAS - GAP_OPEN;
+        o.col_f = colF; o.col_r = colR;
+        out[task] = o;
+    }
+}
+}  // namespace svp

@@ -1,0 +1,310 @@
+// K3/K4: quality-weighted pileup, vote, consensus rewrite and the polish_to_perfection state machine.
+// One block per variant (window); atomic-free: thread p owns reference position p and adds the reads'
+// contributions in pair order (read, then mate), which is the order of the reference's sequential loops
+// (/root/reference/include/sviper/polishing.h:133-148), so every fp64 sum is bit-identical.
+// fp64 products and sums use __dmul_rn/__dadd_rn: no FMA contraction (the reference build has no -march).
+//
+//   mappQ stats            polishing.h:174-195       (exact in any order: multiples of 0.5)
+//   proper pair            mapping.h:164-173, config.h:101-109
+//   fill_profile           polishing.h:54-172        (records come from k2_traceback_kernel)
+//   consensus_from_profile polishing.h:236-293, basic/alphabet_profile.h:295-313, config.h:128-133
+//   loop control           polishing.h:319-346
+#pragma once
+#include <cub/block/block_scan.cuh>
+#include <cub/block/block_reduce.cuh>
+#include "common.cuh"
+#include "k1_trace.cuh"
+
+namespace svp
+{
+constexpr int K3_THREADS = 256;
+
+struct VarDesc
+{
+    int32_t n_pairs;
+    int32_t pair_base;      // first entry of this variant in pair_task (2 per pair: read, mate or -1)
+    int64_t cons_off;       // byte offset of this variant's consensus buffers
+    int32_t Lcap;           // capacity of a consensus buffer
+    int32_t flank;
+    double bq_mean, ins_mean, ins_sd, min_cov;
+    int64_t prof_off;       // first view column of this variant in the profile buffers
+    int32_t prof_cap;
+    int32_t win_id;         // window slot in the packed store
+};
+
+struct VarState
+{
+    int32_t L;              // current consensus length
+    int32_t fix_indels;
+    int32_t rounds;
+    int32_t done;
+    int32_t err;
+    uint32_t subst, ins, del;
+    double mappq_mean;
+    int32_t Lp;             // view columns of the last round
+    int32_t cur;            // which consensus buffer is current (0/1)
+};
+
+struct K3Buffers
+{
+    uint8_t *cons[2];       // ping-pong consensus bytes (0..4)
+    int32_t *inslen;        // per reference position (indexed like cons)
+    int32_t *voff;
+    double *profile;        // view columns x 6
+    uint32_t *cov;
+    uint8_t *isgap;
+    uint8_t *decision;      // per view column: 0..4 emit that base, 255 emit nothing
+    uint8_t *proper;        // per pair
+};
+
+__device__ __forceinline__ int oriented_base(const SeqStore &reads, int rid, int R, int is_rc, int q)
+{
+    int src = is_rc ? (R - 1 - q) : q;
+    int b = seq_base(reads, reads.off32[rid], src);
+    return is_rc ? ((b < 4) ? 3 - b : 4) : b;
+}
+
+__global__ void __launch_bounds__(K3_THREADS) k3_pileup_vote_kernel(
+    const VarDesc *__restrict__ descs, VarState *__restrict__ states, const int32_t *__restrict__ pair_task,
+    const AlnOut *__restrict__ alns, const TracePlan *__restrict__ plans, RecArrays rec,
+    const int64_t *__restrict__ rec_off, SeqStore reads, const uint8_t *__restrict__ read_quals,
+    const int64_t *__restrict__ qual_off, K3Buffers buf, int force_single_round)
+{
+    const int v = blockIdx.x, tid = threadIdx.x;
+    VarState st = states[v];
+    if (st.done) return;
+    const VarDesc d = descs[v];
+    const int L = st.L, P = d.n_pairs, flank = d.flank;
+    const uint8_t *cons = buf.cons[st.cur] + d.cons_off;
+    uint8_t *next = buf.cons[st.cur ^ 1] + d.cons_off;
+    int32_t *inslen = buf.inslen + d.cons_off;
+    int32_t *voff = buf.voff + d.cons_off;
+    double *profile = buf.profile + d.prof_off * 6;
+    uint32_t *cov = buf.cov + d.prof_off;
+    uint8_t *isgap = buf.isgap + d.prof_off;
+    uint8_t *decision = buf.decision + d.prof_off;
+    uint8_t *proper = buf.proper + d.pair_base / 2;
+    const int32_t *pt = pair_task + d.pair_base;
+
+    typedef cub::BlockReduce<long long, K3_THREADS> BR;
+    typedef cub::BlockScan<int, K3_THREADS> BS;
+    __shared__ union { typename BR::TempStorage r; typename BS::TempStorage s; } tmp;
+    __shared__ long long sh_ll;
+    __shared__ int sh_i[4];
+
+    // ---- 1. proper pairs + mappQ mean -------------------------------------------------------
+    const double rs = fmax(0.0, d.ins_mean - 3 * d.ins_sd);
+    const double re = fmin(d.ins_mean + 3 * d.ins_mean, d.ins_mean + 3 * d.ins_sd);
+    long long msum = 0;
+    int aerr = 0;
+    for (int i = tid; i < P; i += K3_THREADS)
+    {
+        int t1 = pt[2 * i], t2 = pt[2 * i + 1];
+        AlnOut a = alns[t1];
+        aerr |= a.err;
+        uint8_t pr = 0;
+        if (t2 >= 0)
+        {
+            AlnOut b = alns[t2];
+            aerr |= b.err;
+            msum += a.mapq + b.mapq;
+            if (!a.is_rc && b.is_rc) { int dd = b.lead - a.endpos; pr = (dd > rs) && (dd < re); }
+            else if (a.is_rc && !b.is_rc) { int dd = a.lead - b.endpos; pr = (dd > rs) && (dd < re); }
+        }
+        else
+            msum += 2 * a.mapq;
+        proper[i] = pr;
+    }
+    msum = BR(tmp.r).Sum(msum);
+    if (tid == 0) sh_ll = msum;
+    aerr = __syncthreads_or(aerr);
+    const double mappq = (P > 0) ? ((double)sh_ll * 0.5) / (double)P : st.mappq_mean;
+    if (aerr) { if (tid == 0) { states[v].err = 10 + aerr; states[v].done = 1; } return; }
+    __syncthreads();
+
+    // ---- 2. insertion sub-profile lengths per reference position ---------------------------
+    for (int p = tid; p < L; p += K3_THREADS)
+    {
+        int il = 0;
+        for (int i = 0; i < P; ++i)
+        {
+            if (!proper[i]) continue;
+#pragma unroll
+            for (int w = 0; w < 2; ++w)
+            {
+                int t = pt[2 * i + w];
+                if (t < 0) continue;
+                int p0 = alns[t].p0, n = alns[t].n;
+                if (p < p0 || p >= p0 + n) continue;
+                int64_t r = rec_off[t] + (p - p0);
+                uint8_t cd = rec.code[r];
+                int l = rec.inslen[r];
+                if (l > il) il = l;
+                if ((cd & 8u) && il < 1) il = 1;
+            }
+        }
+        inslen[p] = il;
+    }
+    __syncthreads();
+    // ---- 3. view offsets: exclusive scan of inslen[p] + 1 ------------------------------------
+    {
+        int carry = 0;
+        for (int base = 0; base < L; base += K3_THREADS)
+        {
+            int p = base + tid;
+            int x = (p < L) ? inslen[p] + 1 : 0, ex, tot;
+            BS(tmp.s).ExclusiveSum(x, ex, tot);
+            if (p < L) voff[p] = carry + ex;
+            carry += tot;
+            __syncthreads();
+        }
+        if (tid == 0) sh_i[0] = carry;
+    }
+    __syncthreads();
+    const int Lp = sh_i[0];
+    if (Lp > d.prof_cap) { if (tid == 0) { states[v].err = 4; states[v].done = 1; } return; }
+
+    // ---- 4. pileup + vote per reference position ---------------------------------------------
+    const double qq = __dmul_rn(d.bq_mean, mappq);
+    const int fix = st.fix_indels;
+    unsigned n_sub = 0, n_ins = 0, n_del = 0;
+    auto vote = [&](const double *c, unsigned cv, int gap, int base) -> int {
+        // returns the base to emit (0..4) or 255; updates the counters
+        if (!fix && gap) return 255;
+        int idx = 0; double mx = c[0];
+#pragma unroll
+        for (int k = 1; k < 6; ++k) if (c[k] > mx) { idx = k; mx = c[k]; }
+        double half = (double)cv / 2;
+        double thr = __dmul_rn((d.min_cov < half) ? half : d.min_cov, qq);
+        if (!(c[idx] >= thr)) return gap ? 255 : base;
+        if (idx < 5) { if (gap) ++n_ins; else if (base != idx) ++n_sub; return idx; }
+        if (!fix) return gap ? 255 : base;
+        if (!gap) ++n_del;
+        return 255;
+    };
+    for (int p = tid; p < L; p += K3_THREADS)
+    {
+        double m[6] = {0, 0, 0, 0, 0, 0};
+        double gap0 = 0.0;
+        unsigned cv = 0, noins = 0, runs = 0;
+        const int il = inslen[p];
+        for (int i = 0; i < P; ++i)
+        {
+            if (!proper[i]) continue;
+#pragma unroll
+            for (int w = 0; w < 2; ++w)
+            {
+                int t = pt[2 * i + w];
+                if (t < 0) continue;
+                int p0 = alns[t].p0, n = alns[t].n;
+                if (p < p0 || p >= p0 + n) continue;
+                int64_t r = rec_off[t] + (p - p0);
+                uint8_t cd = rec.code[r];
+                double mq = (double)alns[t].mapq;
+                double gw = __dmul_rn(d.bq_mean, mq);
+                if (rec.inslen[r]) ++runs;
+                if (cd & 8u) { gap0 = __dadd_rn(gap0, gw); ++noins; }
+                int sym = cd & 7u;
+                double wgt = (sym < 5) ? __dmul_rn((double)rec.qual[r], mq) : gw;
+                m[sym] = __dadd_rn(m[sym], wgt);
+                ++cv;
+            }
+        }
+        const int col0 = voff[p];
+        const bool ins_in = (p > flank) && (p <= L - flank);
+        // inserted columns in front of p
+        for (int k = 0; k < il; ++k)
+        {
+            double c[6] = {0, 0, 0, 0, 0, gap0};
+            unsigned ck = (k == 0) ? noins : 0;   // ins_cov[k]; noins bookings count in column 0
+            if (runs)
+            {
+                for (int i = 0; i < P; ++i)
+                {
+                    if (!proper[i]) continue;
+#pragma unroll
+                    for (int w = 0; w < 2; ++w)
+                    {
+                        int t = pt[2 * i + w];
+                        if (t < 0) continue;
+                        int p0 = alns[t].p0, n = alns[t].n;
+                        if (p < p0 || p >= p0 + n) continue;
+                        int64_t r = rec_off[t] + (p - p0);
+                        if (rec.inslen[r] <= k) continue;
+                        int rid = plans[t].read_id, R = reads.len[rid], rc = alns[t].is_rc;
+                        int q = rec.insq[r] + k;
+                        int b = oriented_base(reads, rid, R, rc, q);
+                        int ql = read_quals[qual_off[rid] + (rc ? R - 1 - q : q)];
+                        c[b] = __dadd_rn(c[b], __dmul_rn((double)ql, (double)alns[t].mapq));
+                        ++ck;
+                    }
+                }
+            }
+            if (k >= 1) ck += noins;   // polishing.h:159-160
+            int col = col0 + k;
+#pragma unroll
+            for (int s = 0; s < 6; ++s) profile[(size_t)col * 6 + s] = c[s];
+            cov[col] = ck; isgap[col] = 1;
+            decision[col] = ins_in ? (uint8_t)vote(c, ck, 1, -1) : 255;
+        }
+        {
+            int col = col0 + il;
+#pragma unroll
+            for (int s = 0; s < 6; ++s) profile[(size_t)col * 6 + s] = m[s];
+            cov[col] = cv; isgap[col] = 0;
+            int base = cons[p];
+            decision[col] = (p >= flank && p < L - flank) ? (uint8_t)vote(m, cv, 0, base) : 255;
+        }
+    }
+    {
+        typedef cub::BlockReduce<long long, K3_THREADS> BR2;
+        long long pk = ((long long)n_sub) | ((long long)n_ins << 20) | ((long long)n_del << 40);
+        __syncthreads();
+        pk = BR(tmp.r).Sum(pk);
+        if (tid == 0) sh_ll = pk;
+    }
+    __syncthreads();
+    // ---- 5. compaction: new consensus = prefix + emitted + suffix ----------------------------
+    const int vb = voff[flank] + inslen[flank];                 // column of base `flank`
+    const int ve = voff[L - flank] + inslen[L - flank];         // column of base L - flank
+    int carry = flank;
+    for (int i = tid; i < flank; i += K3_THREADS) next[i] = cons[i];
+    for (int base = vb; base < ve; base += K3_THREADS)
+    {
+        int col = base + tid;
+        int dcs = (col < ve) ? decision[col] : 255;
+        int x = (dcs != 255), ex, tot;
+        BS(tmp.s).ExclusiveSum(x, ex, tot);
+        if (x && carry + ex < d.Lcap) next[carry + ex] = (uint8_t)dcs;
+        carry += tot;
+        __syncthreads();
+    }
+    const int newL = carry + flank;
+    if (newL > d.Lcap) { if (tid == 0) { states[v].err = 5; states[v].done = 1; } return; }
+    for (int i = tid; i < flank; i += K3_THREADS) next[carry + i] = cons[L - flank + i];
+    __syncthreads();
+    // ---- 6. convergence + loop control (polishing.h:327-343) ---------------------------------
+    int diff = (newL != L);
+    if (!diff)
+        for (int i = tid; i < L; i += K3_THREADS) diff |= (next[i] != cons[i]);
+    diff = __syncthreads_or(diff);
+    if (tid == 0)
+    {
+        long long pk = sh_ll;
+        st.subst += (unsigned)(pk & 0xfffff); st.ins += (unsigned)((pk >> 20) & 0xfffff); st.del += (unsigned)(pk >> 40);
+        st.mappq_mean = mappq;
+        st.rounds += 1;
+        st.Lp = Lp;
+        st.L = newL;
+        st.cur ^= 1;
+        if (force_single_round) st.done = 1;
+        else if (!st.fix_indels)
+        {
+            if (!diff || st.rounds >= 20) st.fix_indels = 1;   // phase 2 always starts with one more round
+            if (st.rounds >= 30) st.done = 1;
+        }
+        else if (!diff || st.rounds >= 30) st.done = 1;
+        states[v] = st;
+    }
+}
+}  // namespace svp

@@ -1,0 +1,214 @@
+// K5: final alignment of the polished sequence (V, rows) against the reference part (H, columns):
+// seqan::globalAlignment(gapsRef, gapsSeq, Score<double>(MM,MX,GE,GO), AlignConfig<0,0,0,0>, ConvexGaps)
+// + getCigarString (/root/reference/include/sviper/sviper.h:452-466).
+//
+// The recurrence is the vendored fork's convex-gap formula, replayed op for op in IEEE fp64
+// (seqan/align/dp_formula_convex.h:62-141, :276-380; cell = {S,H,V,Hlen,Vlen}, dp_cell_convex.h:58-67):
+//   ext = X + min(GE, GO / len_prev)   (X = H or V of the predecessor, len_prev its stored gap length)
+//   opn = S_prev + GO;  tie -> extension;  len = extension ? len_prev + 1 : 1
+// with "infinity" = numeric_limits<double>::min()/2, a POSITIVE denormal (dp_cell.h:137-145) that the
+// first row/column and never-opened gaps start from. min(GE, GO/len) comes from a table computed with the
+// same IEEE division on the host (len is an integer-valued double in the reference), and the first
+// row/column (Horizontal/Vertical recursion) is the same host-computed chain for every job.
+// Compile with -fmad=false; denormals are never flushed (no -ftz).
+//
+// Mapping: one block per job, thread T owns K5_RPL consecutive rows, block-wide wavefront over columns
+// (thread T works on column t-T at step t), bottom rows handed down through shared memory, one
+// __syncthreads per step. Sequences longer than K5_THREADS*K5_RPL rows run as successive row bands with
+// the band's bottom row kept in global memory. Trace: 4 bits per cell as in k1_trace.cuh.
+#pragma once
+#include "common.cuh"
+
+namespace svp
+{
+constexpr int K5_THREADS = 512;
+constexpr int K5_RPL = 8;
+constexpr int K5_BAND = K5_THREADS * K5_RPL;
+
+struct FinalJob
+{
+    const uint8_t *ref;   // H, length n (device)
+    const uint8_t *seq;   // V, length m (device)
+    int32_t n, m;
+    int64_t trace_off;    // u32 words: n * row_threads
+    int32_t row_threads;  // nbands * K5_THREADS
+    int64_t bnd_off;      // per-column band boundary (n + 1 entries)
+    int32_t valid;
+};
+
+struct FinalEnd
+{
+    double S, H, V;
+};
+
+struct K5Tables
+{
+    const double *gapstep;   // gapstep[len] = min(GE, GO / len), len >= 1
+    const double *edge;      // edge[i] = score of cell (i,0) == cell (0,i)
+    int32_t size;
+};
+
+__global__ void __launch_bounds__(K5_THREADS) k5_final_kernel(const FinalJob *__restrict__ jobs, K5Tables tb,
+                                                             double MM, double MX, double GO, double INF,
+                                                             uint32_t *__restrict__ trace, double *__restrict__ bndS,
+                                                             double *__restrict__ bndV, int32_t *__restrict__ bndVL,
+                                                             FinalEnd *__restrict__ ends)
+{
+    const FinalJob job = jobs[blockIdx.x];
+    if (!job.valid) return;
+    const int T = threadIdx.x, n = job.n, m = job.m;
+    __shared__ double shS[2][K5_THREADS], shV[2][K5_THREADS];
+    __shared__ int shVL[2][K5_THREADS];
+    uint32_t *tr = trace + job.trace_off;
+    double *bS = bndS + job.bnd_off, *bV = bndV + job.bnd_off;
+    int32_t *bVL = bndVL + job.bnd_off;
+    const int nbands = job.row_threads / K5_THREADS;
+
+    for (int band = 0; band < nbands; ++band)
+    {
+        const int row0 = band * K5_BAND + T * K5_RPL;   // rows row0+1 .. row0+K5_RPL
+        double S[K5_RPL], H[K5_RPL];
+        int HL[K5_RPL], sv[K5_RPL];
+#pragma unroll
+        for (int k = 0; k < K5_RPL; ++k)
+        {
+            int row = row0 + k + 1;
+            S[k] = (row <= m) ? tb.edge[row] : 0.0;
+            H[k] = INF; HL[k] = 1;
+            sv[k] = (row <= m) ? job.seq[row - 1] : 255;
+        }
+        double prev_up = (row0 <= m) ? tb.edge[row0] : 0.0;   // S[row0][0]
+        const bool live = row0 < m;                            // this thread owns at least one real row
+        const int nsteps = n + K5_THREADS - 1;
+        for (int t = 0; t < nsteps; ++t)
+        {
+            const int col = t - T + 1;
+            const int par = t & 1;
+            if (col >= 1 && col <= n && live)
+            {
+                double up_s, up_v; int up_vl;
+                if (T == 0)
+                {
+                    if (band == 0) { up_s = tb.edge[col]; up_v = INF; up_vl = 1; }
+                    else { up_s = bS[col]; up_v = bV[col]; up_vl = bVL[col]; }
+                }
+                else { up_s = shS[par ^ 1][T - 1]; up_v = shV[par ^ 1][T - 1]; up_vl = shVL[par ^ 1][T - 1]; }
+                const int hc = job.ref[col - 1];
+                double diag = prev_up;
+                prev_up = up_s;
+                uint32_t tw = 0;
+#pragma unroll
+                for (int k = 0; k < K5_RPL; ++k)
+                {
+                    double inter = __dadd_rn(diag, (hc == sv[k]) ? MM : MX);
+                    diag = S[k];
+                    double hext = __dadd_rn(H[k], __ldg(tb.gapstep + HL[k]));
+                    double hopn = __dadd_rn(S[k], GO);
+                    uint32_t code;
+                    double hh;
+                    if (hext < hopn) { hh = hopn; HL[k] = 1; code = 0u; } else { hh = hext; HL[k] += 1; code = 1u; }
+                    H[k] = hh;
+                    double vext = __dadd_rn(up_v, __ldg(tb.gapstep + up_vl));
+                    double vopn = __dadd_rn(up_s, GO);
+                    if (vext < vopn) { up_v = vopn; up_vl = 1; } else { up_v = vext; up_vl += 1; code |= 2u; }
+                    double gap; uint32_t gsel;
+                    if (up_v < hh) { gap = hh; gsel = 8u; } else { gap = up_v; gsel = 4u; }
+                    double sn;
+                    if (inter < gap) { sn = gap; code |= gsel; } else sn = inter;
+                    if (col == n && row0 + k + 1 == m)
+                    {
+                        FinalEnd e; e.S = sn; e.H = hh; e.V = up_v;
+                        ends[blockIdx.x] = e;
+                        if (up_v == sn) code = (code & 3u) | 4u;        // dp_algorithm_impl.h:1212-1229
+                        else if (hh == sn) code = (code & 3u) | 8u;
+                    }
+                    tw |= code << (4 * k);
+                    S[k] = sn; up_s = sn;
+                }
+                shS[par][T] = up_s; shV[par][T] = up_v; shVL[par][T] = up_vl;
+                if (T == K5_THREADS - 1 && band + 1 < nbands) { bS[col] = up_s; bV[col] = up_v; bVL[col] = up_vl; }
+                tr[(size_t)(col - 1) * job.row_threads + band * K5_THREADS + T] = tw;
+            }
+            __syncthreads();
+        }
+        __threadfence_block();
+        __syncthreads();
+    }
+}
+
+// traceback + run-length CIGAR (seqan/bam_io/cigar.h:354-420 with the D->N rule disabled, sviper.h:466)
+struct CigarOut
+{
+    int32_t n_cigar;
+    int32_t stored;      // elements actually written (<= cap)
+    double score;
+};
+
+__global__ void k5_traceback_kernel(const FinalJob *__restrict__ jobs, int njobs, const uint32_t *__restrict__ trace,
+                                    const FinalEnd *__restrict__ ends, double INF, char *__restrict__ cig_op,
+                                    uint32_t *__restrict__ cig_cnt, int cap, CigarOut *__restrict__ out)
+{
+    int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= njobs) return;
+    const FinalJob job = jobs[j];
+    if (!job.valid) return;
+    char *op = cig_op + (size_t)j * cap;
+    uint32_t *cnt = cig_cnt + (size_t)j * cap;
+    const uint32_t *tr = trace + job.trace_off;
+    int ne = 0;          // elements emitted (reverse order)
+    char last = 0; uint32_t run = 0;
+    auto emit = [&](char c, uint32_t k) {
+        if (k == 0) return;
+        if (c == last) { run += k; return; }
+        if (run) { if (ne < cap) { op[ne] = last; cnt[ne] = run; } ++ne; }
+        last = c; run = k;
+    };
+    CigarOut o;
+    int col = job.n, row = job.m;
+    if (!(ends[j].S > INF))
+    {
+        // the scout never leaves its default cell (dp_scout.h:168-180): n x 'D' then m x 'I'
+        emit('I', (uint32_t)job.m); emit('D', (uint32_t)job.n);
+        col = 0; row = 0;
+        o.score = INF;
+    }
+    else
+        o.score = ends[j].S;
+    auto codeat = [&](int c, int r) -> uint32_t {
+        int slot = r - 1;
+        uint32_t w = tr[(size_t)(c - 1) * job.row_threads + (slot >> 3)];
+        return (w >> (4 * (slot & 7))) & 15u;
+    };
+    while (col > 0 && row > 0)
+    {
+        uint32_t code = codeat(col, row), sel = code >> 2;
+        if (sel == 0) { emit('M', 1); --col; --row; }
+        else if (sel == 1)
+        {
+            if (code & 2u)
+                while ((code & 2u) && row != 1) { --row; code = codeat(col, row); emit('I', 1); }
+            --row; emit('I', 1);
+        }
+        else
+        {
+            if (code & 1u)
+                while ((code & 1u) && col != 1) { --col; code = codeat(col, row); emit('D', 1); }
+            --col; emit('D', 1);
+        }
+    }
+    emit('I', (uint32_t)row);
+    emit('D', (uint32_t)col);
+    if (run) { if (ne < cap) { op[ne] = last; cnt[ne] = run; } ++ne; }
+    o.n_cigar = ne;
+    int st = ne < cap ? ne : cap;
+    o.stored = st;
+    // reverse the stored prefix in place (if truncated the caller only gets n_cigar right)
+    if (ne <= cap)
+        for (int a = 0, b = ne - 1; a < b; ++a, --b)
+        {
+            char c = op[a]; op[a] = op[b]; op[b] = c;
+            uint32_t x = cnt[a]; cnt[a] = cnt[b]; cnt[b] = x;
+        }
+    out[j] = o;
+}
+}  // namespace svp
