@@ -133,6 +133,10 @@ typedef struct
 
 int svp_polish_batch(svp_ctx *ctx, int32_t n_variants, const svp_window_in *in, svp_result *out);
 
+/* Re-runs the last svp_polish_batch (every round and the final alignment) from its HBM-resident inputs;
+ * nothing is copied from or to the host. Used by bench.py for the device-resident throughput. */
+int svp_polish_rerun(svp_ctx *ctx);
+
 /* Final alignment only: ref_part[i] (H) vs seq[i] (V), Score<double>(90000,-80000,-1,-100000), ConvexGaps. */
 typedef struct
 {

@@ -53,7 +53,7 @@ class FinalIn(C.Structure):
 
 
 EXPORTS = ["svp_create", "svp_destroy", "svp_last_error", "svp_version", "svp_align_batch", "svp_align_rerun",
-           "svp_polish_batch", "svp_final_align_batch", "svp_assign_quality", "svp_submit_polish", "svp_wait_any",
+           "svp_polish_batch", "svp_polish_rerun", "svp_final_align_batch", "svp_assign_quality", "svp_submit_polish", "svp_wait_any",
            "svp_debug_round", "svp_probe_dpx", "svp_stats"]
 
 _lib = None
@@ -79,6 +79,7 @@ def lib():
         L.svp_align_batch.argtypes = [C.c_void_p, C.POINTER(AlignIn), C.POINTER(AlignOut), C.c_int]
         L.svp_align_rerun.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_float)]
         L.svp_polish_batch.argtypes = [C.c_void_p, C.c_int32, C.POINTER(WindowIn), C.POINTER(Result)]
+        L.svp_polish_rerun.argtypes = [C.c_void_p]
         L.svp_final_align_batch.argtypes = [C.c_void_p, C.c_int32, C.POINTER(FinalIn), C.POINTER(Result)]
         L.svp_assign_quality.restype = C.c_double
         L.svp_assign_quality.argtypes = [C.c_int32, C.c_int32]
@@ -219,6 +220,9 @@ class Context:
                 d["cigar"] = [(cop.raw[k:k + 1].decode(), int(ccnt[k])) for k in range(r.n_cigar)]
             out.append(d)
         return out
+
+    def polish_rerun(self):
+        self._check(self.L.svp_polish_rerun(self.h), "svp_polish_rerun")
 
     def final_align_batch(self, pairs, cigar_cap=4096):
         keep = []

@@ -67,6 +67,9 @@ void svp_destroy(svp_ctx *ctx)
                       &ctx->ftrace, &ctx->fbndS, &ctx->fbndV, &ctx->fbndVL, &ctx->fends, &ctx->fcig_op, &ctx->fcig_cnt,
                       &ctx->fcig_out, &ctx->gapstep, &ctx->edge};
     for (DevBuf *b : bufs) b->release();
+    ctx->cons_init.release();
+    delete ctx->resident;
+    for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
     cudaEventDestroy(ctx->ev0);
     cudaEventDestroy(ctx->ev1);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
@@ -188,10 +191,11 @@ int svp_probe_dpx(svp_ctx *ctx, double *viaddmax_lane_ops, double *vimax3_lane_o
 int svp_stats(svp_ctx *ctx, int32_t *n_launches, double *ms_by_kernel, int reset)
 {
     if (!ctx) return SVP_ERR_ARG;
+    resolve_timers(ctx);
     if (n_launches) *n_launches = ctx->n_launches;
     if (ms_by_kernel) for (int i = 0; i < ST_N; ++i) ms_by_kernel[i] = ctx->ms[i];
     if (reset == 1) { ctx->n_launches = 0; for (int i = 0; i < ST_N; ++i) ctx->ms[i] = 0; }
-    if (reset == 2) ctx->timing = true;    // enable per-kernel CUDA-event timing (synchronises after each kernel)
+    if (reset == 2) ctx->timing = true;    // enable per-kernel CUDA-event timing (events resolved lazily, no extra syncs)
     if (reset == 3) ctx->timing = false;
     return SVP_OK;
 }

@@ -44,6 +44,9 @@ struct DevSeqs
     }
 };
 
+struct PolishLayout;
+struct FinalSpec;
+
 struct svp_ctx
 {
     int device = 0;
@@ -54,6 +57,9 @@ struct svp_ctx
     int n_launches = 0;
     double ms[ST_N] = {0};
     bool timing = false;
+    std::vector<cudaEvent_t> ev_pool;
+    std::vector<int> ev_slot;
+    size_t ev_used = 0;
     size_t arena_budget = (size_t)96 << 30;
     int full_window = 0;   // debug: trace the whole window instead of the provable sub-window
 
@@ -66,7 +72,9 @@ struct svp_ctx
     DevBuf rec_code, rec_qual, rec_inslen, rec_insq;
     int64_t E_total = 0;
     // ---- polish pipeline ----
-    DevBuf descs, states, pair_task, cons0, cons1, inslen, voff, profile, cov, isgap, decision, proper;
+    DevBuf descs, states, pair_task, cons0, cons1, inslen, voff, profile, cov, isgap, decision, proper, cons_init;
+    struct PolishLayout *resident = nullptr;   // last svp_polish_batch, kept for svp_polish_rerun
+    int resident_nv = 0;
     // ---- final alignment ----
     DevBuf fjobs, fref, fseq, ftrace, fbndS, fbndV, fbndVL, fends, fcig_op, fcig_cnt, fcig_out, gapstep, edge;
     int table_size = 0;
