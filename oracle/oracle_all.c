@@ -57,6 +57,39 @@ int orc_align_batch(int ntasks, const uint8_t *rb, const uint8_t *rq, const int3
     return 0;
 }
 
+/* ---- whole hot path for nv variants (polish_to_perfection + final alignment), one OpenMP thread per
+ * variant like the reference's loop at src/sviper.cpp:43-47. Per-variant inputs are arrays of pointers.
+ * n_cigar[v] receives the number of CIGAR elements, rounds[v] the rounds. CPU baseline for bench.py. ---- */
+int orc_polish_many(int nv, const orc_config *cfgs, const int *np,
+                    const uint8_t **b1, const uint8_t **q1, const int32_t **off1,
+                    const uint8_t **b2, const uint8_t **q2, const int32_t **off2,
+                    const uint8_t **cons, const int *L, const uint8_t **refp, const int *refL,
+                    int *n_cigar, int *rounds)
+{
+    int v;
+#pragma omp parallel for schedule(dynamic, 1)
+    for (v = 0; v < nv; ++v)
+    {
+        orc_config c = cfgs[v];
+        int cap = 2 * L[v] + 4096, covlen = 0, n, nops = 0, k;
+        uint8_t *out = (uint8_t *)malloc((size_t)cap);
+        n = orc_polish_to_perfection(&c, np[v], b1[v], q1[v], off1[v], b2[v], q2[v], off2[v], cons[v], L[v], out, cap,
+                                     NULL, 0, &covlen);
+        rounds[v] = (int)c.rounds;
+        n_cigar[v] = 0;
+        if (n > 0 && refp && refp[v])
+        {
+            char *ops = (char *)malloc((size_t)n + refL[v] + 2);
+            char last = 0;
+            orc_align_convex(refp[v], refL[v], out, n, 90000.0, -80000.0, -1.0, -100000.0, ops, &nops);
+            for (k = 0; k < nops; ++k) if (ops[k] != last) { ++n_cigar[v]; last = ops[k]; }
+            free(ops);
+        }
+        free(out);
+    }
+    return 0;
+}
+
 int orc_num_threads(void)
 {
 #ifdef _OPENMP
