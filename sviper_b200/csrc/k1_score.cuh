@@ -41,7 +41,8 @@ __global__ void __launch_bounds__(128) k1_score_kernel(const int32_t *__restrict
                                                        const int32_t *__restrict__ task_win,
                                                        const int32_t *__restrict__ task_idx, int ntasks,
                                                        const uint8_t *__restrict__ win_done,
-                                                       SeqStore reads, SeqStore wins, ScoreOut *__restrict__ out)
+                                                       SeqStore reads, SeqStore wins, ScoreOut *__restrict__ out,
+                                                       uint32_t one /* always 1; opaque to the compiler */)
 {
     using Sh = K1Shape<RPL>;
     constexpr int G = K1_G, NSLOT = Sh::NSLOT, PST = Sh::PST;
@@ -121,8 +122,9 @@ __global__ void __launch_bounds__(128) k1_score_kernel(const int32_t *__restrict
                 ww = __ldg(w2p + (jj >> 4));
                 if ((jj & 31) == 0) wn = __ldg(wnp + (jj >> 5));
             }
-            int c = (ww >> ((jj & 15) * 2)) & 3;
-            if ((wn >> (jj & 31)) & 1) c = 4;
+            // consume one base: the packer stores 0 in the 2-bit plane under an N, so c = c2 + 4*n is 0..4
+            const int c = (int)(ww & 3u) + (int)((wn & 1u) << 2);
+            ww >>= 2; wn >>= 1;
             const uint32_t *pr = prof + c * PST + g;
             uint32_t diag = prev_up;
             prev_up = r_so;
@@ -135,16 +137,21 @@ __global__ void __launch_bounds__(128) k1_score_kernel(const int32_t *__restrict
                 h[k] = __viaddmax_s16x2(h[k], GE2, so[k]);
                 up_v = __viaddmax_s16x2(up_v, GE2, up_so);
                 uint32_t s = __vimax3_s16x2(inter, h[k], up_v);
-                so[k] = s + GO2;
+                so[k] = s * one + GO2;   // IMAD with a runtime 1: keeps this add off the ALU/DPX pipe
                 up_so = so[k];
             }
             out_so = up_so; out_v = up_v;
             if (g == G - 1)
             {
-                // strict improvement only: the leftmost maximum wins (dp_scout.h:173). Halves are biased positive.
-                if ((up_so & 0xffffu) > (best & 0xffffu)) colF = jj + 1;
-                if ((up_so >> 16) > (best >> 16)) colR = jj + 1;
-                best = __vmaxs2(best, up_so);
+                // strict improvement only: the leftmost maximum wins (dp_scout.h:173). Improvements are rare
+                // (a handful per task), so the per-half bookkeeping sits behind a branch.
+                const uint32_t m = __vmaxs2(best, up_so);
+                if (m != best)
+                {
+                    if ((up_so & 0xffffu) > (best & 0xffffu)) colF = jj + 1;   // halves are biased positive
+                    if ((up_so >> 16) > (best >> 16)) colR = jj + 1;
+                    best = m;
+                }
             }
         }
     }
