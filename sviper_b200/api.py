@@ -200,17 +200,26 @@ class Context:
         r.cigar_op = C.cast(cop, C.c_char_p); r.cigar_cnt = _p(ccnt, u32p); r.cigar_cap = cigar_cap
         return r, pol, cov, cop, ccnt
 
-    def polish_batch(self, variants, with_final=True):
+    def prepare(self, variants, with_final=True):
+        """Builds the svp_window_in / svp_result arrays for a batch once (host buffers, as the reference holds its
+        reads in memory before calling polish_to_perfection). run_prepared() is then the bare C-ABI call."""
         keep = []
         n = len(variants)
         win = (WindowIn * n)(*[self.make_window(v, keep, with_final) for v in variants])
-        res_parts = [self.make_result(len(v["consensus"]) * 2 + 4096, keep) for v in variants]
-        res = (Result * n)(*[p[0] for p in res_parts])
-        self._check(self.L.svp_polish_batch(self.h, n, win, res), "svp_polish_batch")
+        parts = [self.make_result(len(v["consensus"]) * 2 + 4096, keep) for v in variants]
+        res = (Result * n)(*[p[0] for p in parts])
+        h2d = sum(len(k[0]) + len(k[2]) + len(k[3]) + len(k[5]) + len(k[6]) + (len(k[7]) if k[7] is not None else 0)
+                  for k in keep if len(k) == 8)
+        return dict(n=n, win=win, res=res, parts=parts, keep=keep, h2d_bytes=int(h2d))
+
+    def run_prepared(self, pb):
+        self._check(self.L.svp_polish_batch(self.h, pb["n"], pb["win"], pb["res"]), "svp_polish_batch")
+
+    def collect(self, pb):
         out = []
-        for i in range(n):
-            r = res[i]
-            _, pol, cov, cop, ccnt = res_parts[i]
+        for i in range(pb["n"]):
+            r = pb["res"][i]
+            _, pol, cov, cop, ccnt = pb["parts"][i]
             if r.status != 0:
                 raise RuntimeError("variant %d failed with status %d" % (i, r.status))
             d = dict(polished=pol[:r.polished_len].copy(), rounds=r.rounds, subst=r.substituted_bases,
@@ -220,6 +229,11 @@ class Context:
                 d["cigar"] = [(cop.raw[k:k + 1].decode(), int(ccnt[k])) for k in range(r.n_cigar)]
             out.append(d)
         return out
+
+    def polish_batch(self, variants, with_final=True):
+        pb = self.prepare(variants, with_final)
+        self.run_prepared(pb)
+        return self.collect(pb)
 
     def polish_rerun(self):
         self._check(self.L.svp_polish_rerun(self.h), "svp_polish_rerun")

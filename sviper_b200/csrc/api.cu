@@ -44,6 +44,7 @@ svp_ctx *svp_create(int cuda_device, void *cuda_stream)
     }
     cudaEventCreate(&ctx->ev0);
     cudaEventCreate(&ctx->ev1);
+    if (cudaHostAlloc((void **)&ctx->h_active, 64, cudaHostAllocDefault) != cudaSuccess) { delete ctx; return nullptr; }
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) ctx->arena_budget = (size_t)(free_b * 0.6);
     const char *fw = getenv("SVP_FULL_WINDOW");
@@ -67,7 +68,10 @@ void svp_destroy(svp_ctx *ctx)
                       &ctx->ftrace, &ctx->fbndS, &ctx->fbndV, &ctx->fbndVL, &ctx->fends, &ctx->fcig_op, &ctx->fcig_cnt,
                       &ctx->fcig_out, &ctx->gapstep, &ctx->edge};
     for (DevBuf *b : bufs) b->release();
-    ctx->cons_init.release();
+    ctx->cons_init.release(); ctx->states_init.release();
+    ctx->win_done.release(); ctx->active.release(); ctx->gather_desc.release(); ctx->gather_out.release();
+    ctx->stage.release();
+    if (ctx->h_active) cudaFreeHost(ctx->h_active);
     delete ctx->resident;
     for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
     cudaEventDestroy(ctx->ev0);
@@ -81,7 +85,8 @@ const char *svp_last_error(const svp_ctx *ctx) { return ctx ? ctx->err.c_str() :
 int svp_align_batch(svp_ctx *ctx, const svp_align_in *in, svp_align_out *out, int with_traceback)
 {
     if (!ctx || !in || !out) return SVP_ERR_ARG;
-    CK(cudaSetDevice(ctx->device));
+    int rc = begin_call(ctx);
+    if (rc) return rc;
     std::vector<int64_t> roff(in->n_reads + 1), woff(in->n_windows + 1);
     std::vector<int32_t> rlen(in->n_reads);
     for (int i = 0; i <= in->n_reads; ++i) roff[i] = in->read_off[i];
@@ -91,7 +96,7 @@ int svp_align_batch(svp_ctx *ctx, const svp_align_in *in, svp_align_out *out, in
         if (in->task_read[t] < 0 || in->task_read[t] >= in->n_reads || in->task_win[t] < 0 ||
             in->task_win[t] >= in->n_windows || in->win_off[in->task_win[t] + 1] - in->win_off[in->task_win[t]] < 1)
             return svp_fail_msg(ctx, SVP_ERR_ARG, "task refers to a missing read/window");
-    int rc = upload_seqs(ctx, ctx->reads, in->n_reads, in->read_bases, roff.data(), nullptr, true);
+    rc = upload_seqs(ctx, ctx->reads, in->n_reads, in->read_bases, roff.data(), nullptr, true);
     if (rc) return rc;
     rc = upload_seqs(ctx, ctx->wins, in->n_windows, in->win_bases, woff.data(), nullptr, true);
     if (rc) return rc;
@@ -100,23 +105,27 @@ int svp_align_batch(svp_ctx *ctx, const svp_align_in *in, svp_align_out *out, in
     rc = run_score_pass(ctx, nullptr);
     if (rc) return rc;
     const int n = in->n_tasks;
-    std::vector<svp::ScoreOut> sc(n);
-    if (n) CK(cudaMemcpyAsync(sc.data(), ctx->score_out.p, (size_t)n * sizeof(svp::ScoreOut), cudaMemcpyDeviceToHost, ctx->stream));
-    std::vector<svp::AlnOut> al;
-    std::vector<uint8_t> ops;
-    std::vector<int64_t> E;
-    if (with_traceback && n)
+    if (n == 0) return SVP_OK;
+    STAGE(sc, svp::ScoreOut, n);
+    CK(cudaMemcpyAsync(sc, ctx->score_out.p, (size_t)n * sizeof(svp::ScoreOut), cudaMemcpyDeviceToHost, ctx->stream));
+    svp::AlnOut *al = nullptr;
+    uint8_t *ops = nullptr;
+    int64_t *E = nullptr;
+    if (with_traceback)
     {
         rc = run_trace_pass(ctx, nullptr, false);
         if (rc) return rc;
-        al.resize(n);
-        CK(cudaMemcpyAsync(al.data(), ctx->alns.p, (size_t)n * sizeof(svp::AlnOut), cudaMemcpyDeviceToHost, ctx->stream));
+        al = ctx->stage.get<svp::AlnOut>(n);
+        if (!al) return svp_fail_msg(ctx, SVP_ERR_CUDA, "cannot allocate pinned staging memory");
+        CK(cudaMemcpyAsync(al, ctx->alns.p, (size_t)n * sizeof(svp::AlnOut), cudaMemcpyDeviceToHost, ctx->stream));
         if (out->ops)
         {
-            E.resize(n + 1);
-            ops.resize((size_t)ctx->E_total + (size_t)n * SVP_MAX_READ_LEN);
-            CK(cudaMemcpyAsync(E.data(), ctx->E.p, (size_t)(n + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
-            CK(cudaMemcpyAsync(ops.data(), ctx->ops.p, ops.size(), cudaMemcpyDeviceToHost, ctx->stream));
+            size_t nops = (size_t)ctx->E_total + (size_t)n * SVP_MAX_READ_LEN;
+            E = ctx->stage.get<int64_t>(n + 1);
+            ops = ctx->stage.get<uint8_t>(nops);
+            if (!E || !ops) return svp_fail_msg(ctx, SVP_ERR_CUDA, "cannot allocate pinned staging memory");
+            CK(cudaMemcpyAsync(E, ctx->E.p, (size_t)(n + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+            CK(cudaMemcpyAsync(ops, ctx->ops.p, nops, cudaMemcpyDeviceToHost, ctx->stream));
         }
     }
     CK(cudaStreamSynchronize(ctx->stream));
@@ -132,7 +141,7 @@ int svp_align_batch(svp_ctx *ctx, const svp_align_in *in, svp_align_out *out, in
         if (out->ops)
         {
             // view columns [lead, endpos): leading 'I's, then the path (stored reversed) without its trailing 'D's
-            const uint8_t *p = ops.data() + E[t] + (int64_t)t * SVP_MAX_READ_LEN;
+            const uint8_t *p = ops + E[t] + (int64_t)t * SVP_MAX_READ_LEN;
             int len = al[t].endpos - al[t].lead, k = 0;
             char *dst = out->ops + (size_t)t * out->ops_cap;
             for (int i = 0; i < al[t].lead_i && k < len; ++i, ++k) if (k < out->ops_cap) dst[k] = 'I';

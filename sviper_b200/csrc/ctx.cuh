@@ -28,6 +28,53 @@ struct DevBuf
     template <typename T> T *as() const { return (T *)p; }
 };
 
+// Pinned host staging: a bump allocator over page-locked blocks. Everything a batch call copies to or from
+// the device goes through it (one cudaMemcpyAsync per array, no per-sequence copies, no pageable staging by
+// the driver). reset() is called at the start of a batch call, after the stream has been synchronised.
+struct HostStage
+{
+    struct Block { char *p; size_t cap; };
+    std::vector<Block> blocks;
+    size_t used = 0;       // bytes used in blocks.back()
+    size_t total_req = 0;  // bytes requested since the last reset (sizes the consolidated block)
+    void *alloc(size_t bytes)
+    {
+        bytes = (bytes + 255) & ~(size_t)255;
+        total_req += bytes;
+        if (blocks.empty() || used + bytes > blocks.back().cap)
+        {
+            size_t cap = bytes > ((size_t)8 << 20) ? bytes : ((size_t)8 << 20);
+            if (!blocks.empty() && cap < blocks.back().cap * 2) cap = blocks.back().cap * 2;
+            char *p = nullptr;
+            if (cudaHostAlloc((void **)&p, cap, cudaHostAllocDefault) != cudaSuccess) return nullptr;
+            blocks.push_back({p, cap});
+            used = 0;
+        }
+        void *r = blocks.back().p + used;
+        used += bytes;
+        return r;
+    }
+    template <typename T> T *get(size_t n) { return (T *)alloc(n * sizeof(T) + sizeof(T)); }
+    void reset()
+    {
+        if (blocks.size() > 1)
+        {
+            // consolidate: one block that holds everything the last call needed
+            for (Block &b : blocks) cudaFreeHost(b.p);
+            blocks.clear();
+            size_t cap = total_req + total_req / 2;
+            char *p = nullptr;
+            if (cudaHostAlloc((void **)&p, cap, cudaHostAllocDefault) == cudaSuccess) blocks.push_back({p, cap});
+        }
+        used = 0; total_req = 0;
+    }
+    void release()
+    {
+        for (Block &b : blocks) cudaFreeHost(b.p);
+        blocks.clear(); used = 0; total_req = 0;
+    }
+};
+
 enum { ST_K1 = 0, ST_K1T, ST_K2, ST_K3, ST_K5, ST_K5TB, ST_PACK, ST_OTHER, ST_N };
 
 // device-resident packed sequences (reads or windows)
@@ -72,12 +119,16 @@ struct svp_ctx
     DevBuf rec_code, rec_qual, rec_inslen, rec_insq;
     int64_t E_total = 0;
     // ---- polish pipeline ----
-    DevBuf descs, states, pair_task, cons0, cons1, inslen, voff, profile, cov, isgap, decision, proper, cons_init;
+    DevBuf descs, states, states_init, pair_task, cons0, cons1, inslen, voff, profile, cov, isgap, decision, proper, cons_init;
     struct PolishLayout *resident = nullptr;   // last svp_polish_batch, kept for svp_polish_rerun
     int resident_nv = 0;
     // ---- final alignment ----
     DevBuf fjobs, fref, fseq, ftrace, fbndS, fbndV, fbndVL, fends, fcig_op, fcig_cnt, fcig_out, gapstep, edge;
     int table_size = 0;
+    // ---- host staging / result gather ----
+    HostStage stage;
+    DevBuf win_done, active, gather_desc, gather_out;
+    int32_t *h_active = nullptr;   // pinned flag the round loop polls
     // ---- scheduler facade ----
     std::vector<uint64_t> q_tag;
     std::vector<const svp_window_in *> q_in;
