@@ -13,9 +13,16 @@
 // (substitution score 0 keeps S == 0 there, which is exactly the free-begin row of
 // AlignConfig<true,false,false,true>), so the read's last row is always the last slot of lane 7.
 //
-// Per cell pair: 1 LDS (query profile), IADD (diag+sub), VIADDMNMX (H), VIADDMNMX (V), VIMNMX3 (S),
-// IADD (S+go) -- no trace, no compares. Values are biased by +0x2000 so that both halves stay positive
-// and plain 32-bit adds never carry between halves.
+// Per cell pair: 1 LDS (query profile), IMAD (diag + sub), 4x VIADDMNMX -- no trace, no compares:
+//   H'   = max(H + ge, So_left)            So := S + go of the cell to the left
+//   M    = max(H' + go, So_diag + sub)     = max(H', diag + sub) + go
+//   V    = max(V_up + ge, M_up)            == max(V_up + ge, So_up): the V_up + go term of So_up = max(M_up, V_up + go)
+//                                          never wins against V_up + ge because ge > go
+//   So   = max(V + go, M)
+// so the only loop-carried dependency down a lane's rows is ONE instruction per row (the V chain); everything
+// else of a column is independent work. (The textbook S = max3(diag+sub, H', V); So = S + go form needs one
+// instruction less on the ALU pipe but chains three dependent instructions per row, which left the pipe idle.)
+// Values are biased by +0x2000 so that both halves stay positive and plain 32-bit adds never carry between halves.
 #pragma once
 #include "common.cuh"
 
@@ -67,7 +74,7 @@ __global__ void __launch_bounds__(128) k1_score_kernel(const int32_t *__restrict
     const int pad = NSLOT - R;   // extra "row 0"s at the top
 
     constexpr uint32_t GE2 = 0xFFFFFFFFu;           // (-1,-1)
-    constexpr uint32_t GO2 = 0u - 0x00060006u;      // 32-bit add of this subtracts 6 from both halves (no borrow)
+    constexpr uint32_t GO2 = 0xFFFAFFFAu;           // (-6,-6), per-half addend of VIADDMNMX
     constexpr uint32_t NEG2 = 0x00010001u;          // "-infinity": biased 1
     constexpr uint32_t ROW0_SO = k1_pk(GAP_OPEN);   // S == 0 plus gap open
 
@@ -87,9 +94,11 @@ __global__ void __launch_bounds__(128) k1_score_kernel(const int32_t *__restrict
 #pragma unroll
         for (int c = 0; c < 5; ++c)
         {
-            uint32_t sf = (row < 1) ? 6u : ((c == rf) ? 7u : 2u);   // sub - go
-            uint32_t sr = (row < 1) ? 6u : ((c == rr) ? 7u : 2u);
-            prof[c * PST + k * G + g] = sf | (sr << 16);
+            // substitution scores of both strands as one 32-bit addend: sf + sr * 65536 (two's complement; the
+            // biased halves never borrow from each other)
+            int sf = (row < 1) ? 0 : ((c == rf) ? MATCH : MISMATCH);
+            int sr = (row < 1) ? 0 : ((c == rr) ? MATCH : MISMATCH);
+            prof[c * PST + k * G + g] = (uint32_t)(sf + sr * 65536);
         }
         int s0 = (row >= 1) ? -(5 + row) : 0;
         so[k] = k1_pk(s0 + GAP_OPEN);
@@ -128,17 +137,18 @@ __global__ void __launch_bounds__(128) k1_score_kernel(const int32_t *__restrict
             const uint32_t *pr = prof + c * PST + g;
             uint32_t diag = prev_up;
             prev_up = r_so;
-            uint32_t up_so = r_so, up_v = r_v;
+            uint32_t up_v = __viaddmax_s16x2(r_v, GE2, r_so);   // first row of the lane: the neighbour's true So
+            uint32_t up_so = r_so;
 #pragma unroll
             for (int k = 0; k < RPL; ++k)
             {
-                uint32_t inter = diag + pr[k * G];
+                const uint32_t interg = diag + pr[k * G];
                 diag = so[k];
                 h[k] = __viaddmax_s16x2(h[k], GE2, so[k]);
-                up_v = __viaddmax_s16x2(up_v, GE2, up_so);
-                uint32_t s = __vimax3_s16x2(inter, h[k], up_v);
-                so[k] = s * one + GO2;   // IMAD with a runtime 1: keeps this add off the ALU/DPX pipe
-                up_so = so[k];
+                const uint32_t m = __viaddmax_s16x2(h[k], GO2, interg);
+                up_so = __viaddmax_s16x2(up_v, GO2, m);
+                so[k] = up_so;
+                if (k + 1 < RPL) up_v = __viaddmax_s16x2(up_v, GE2, m);
             }
             out_so = up_so; out_v = up_v;
             if (g == G - 1)

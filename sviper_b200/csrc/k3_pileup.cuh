@@ -17,7 +17,16 @@
 
 namespace svp
 {
-constexpr int K3_THREADS = 256;
+constexpr int K3_THREADS = 1024;
+constexpr int K3_WARPS = K3_THREADS / 32;
+constexpr int K3_LIST = 512;        // per-warp list of alignments overlapping the warp's 32 positions
+
+// dynamic shared memory of k3_pileup_vote_kernel for a batch whose largest variant has max_pairs pairs
+__host__ __device__ inline size_t k3_smem_bytes(int max_pairs)
+{
+    size_t nt = (size_t)2 * max_pairs + 2;
+    return nt * (8 + 4 * 4) + (size_t)K3_WARPS * K3_LIST * 2 + 64;
+}
 
 struct VarDesc
 {
@@ -68,9 +77,9 @@ __global__ void __launch_bounds__(K3_THREADS) k3_pileup_vote_kernel(
     const VarDesc *__restrict__ descs, VarState *__restrict__ states, const int32_t *__restrict__ pair_task,
     const AlnOut *__restrict__ alns, const TracePlan *__restrict__ plans, RecArrays rec,
     const int64_t *__restrict__ rec_off, SeqStore reads, const uint8_t *__restrict__ read_quals,
-    const int64_t *__restrict__ qual_off, K3Buffers buf, int force_single_round)
+    const int64_t *__restrict__ qual_off, K3Buffers buf, int force_single_round, int max_pairs)
 {
-    const int v = blockIdx.x, tid = threadIdx.x;
+    const int v = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     VarState st = states[v];
     if (st.done) return;
     const VarDesc d = descs[v];
@@ -86,6 +95,17 @@ __global__ void __launch_bounds__(K3_THREADS) k3_pileup_vote_kernel(
     uint8_t *proper = buf.proper + d.pair_base / 2;
     const int32_t *pt = pair_task + d.pair_base;
 
+    // per-alignment metadata of this variant, staged once: entry e = 2 * pair + (0 read | 1 mate), in the
+    // reference's accumulation order (polishing.h:133-148). Alignments that contribute nothing have n == 0.
+    extern __shared__ unsigned char k3_dyn[];
+    const int NTcap = 2 * max_pairs + 2, NT = 2 * P;
+    int64_t *e_roff = (int64_t *)k3_dyn;
+    int32_t *e_p0 = (int32_t *)(e_roff + NTcap);
+    int32_t *e_n = e_p0 + NTcap;
+    int32_t *e_mapq = e_n + NTcap;
+    int32_t *e_task = e_mapq + NTcap;
+    uint16_t *wlist = (uint16_t *)(e_task + NTcap) + (size_t)warp * K3_LIST;
+
     typedef cub::BlockReduce<long long, K3_THREADS> BR;
     typedef cub::BlockScan<int, K3_THREADS> BS;
     __shared__ union { typename BR::TempStorage r; typename BS::TempStorage s; } tmp;
@@ -100,12 +120,12 @@ __global__ void __launch_bounds__(K3_THREADS) k3_pileup_vote_kernel(
     for (int i = tid; i < P; i += K3_THREADS)
     {
         int t1 = pt[2 * i], t2 = pt[2 * i + 1];
-        AlnOut a = alns[t1];
+        AlnOut a = alns[t1], b;
         aerr |= a.err;
         uint8_t pr = 0;
         if (t2 >= 0)
         {
-            AlnOut b = alns[t2];
+            b = alns[t2];
             aerr |= b.err;
             msum += a.mapq + b.mapq;
             if (!a.is_rc && b.is_rc) { int dd = b.lead - a.endpos; pr = (dd > rs) && (dd < re); }
@@ -114,6 +134,10 @@ __global__ void __launch_bounds__(K3_THREADS) k3_pileup_vote_kernel(
         else
             msum += 2 * a.mapq;
         proper[i] = pr;
+        e_task[2 * i] = t1; e_task[2 * i + 1] = t2;
+        e_p0[2 * i] = a.p0; e_n[2 * i] = pr ? a.n : 0; e_mapq[2 * i] = a.mapq; e_roff[2 * i] = rec_off[t1];
+        if (pr) { e_p0[2 * i + 1] = b.p0; e_n[2 * i + 1] = b.n; e_mapq[2 * i + 1] = b.mapq; e_roff[2 * i + 1] = rec_off[t2]; }
+        else { e_p0[2 * i + 1] = 0; e_n[2 * i + 1] = 0; e_mapq[2 * i + 1] = 0; e_roff[2 * i + 1] = 0; }
     }
     msum = BR(tmp.r).Sum(msum);
     if (tid == 0) sh_ll = msum;
@@ -122,28 +146,48 @@ __global__ void __launch_bounds__(K3_THREADS) k3_pileup_vote_kernel(
     if (aerr) { if (tid == 0) { states[v].err = 10 + aerr; states[v].done = 1; } return; }
     __syncthreads();
 
-    // ---- 2. insertion sub-profile lengths per reference position ---------------------------
-    for (int p = tid; p < L; p += K3_THREADS)
-    {
-        int il = 0;
-        for (int i = 0; i < P; ++i)
+    // the warp's 32 consecutive positions share (almost) the same covering alignments: compact them once,
+    // order preserved. Returns the list length, or -1 when it does not fit (then every entry is visited).
+    auto build_list = [&](int lo, int hi) -> int {
+        int cnt = 0;
+        for (int base = 0; base < NT; base += 32)
         {
-            if (!proper[i]) continue;
-#pragma unroll
-            for (int w = 0; w < 2; ++w)
+            int e = base + lane;
+            bool hit = false;
+            if (e < NT) { int n = e_n[e], p0 = e_p0[e]; hit = n > 0 && p0 <= hi && p0 + n > lo; }
+            unsigned m = __ballot_sync(0xffffffffu, hit);
+            if (hit) { int at = cnt + __popc(m & ((1u << lane) - 1)); if (at < K3_LIST) wlist[at] = (uint16_t)e; }
+            cnt += __popc(m);
+        }
+        __syncwarp();
+        return (cnt <= K3_LIST && NT <= 65535) ? cnt : -1;
+    };
+
+    // ---- 2. insertion sub-profile lengths per reference position ---------------------------
+    for (int base = 0; base < L; base += K3_THREADS)
+    {
+        const int p = base + tid;
+        const int lo = base + warp * 32;
+        if (lo >= L) continue;                       // whole warp out of range (warp-uniform)
+        const int nl = build_list(lo, min(lo + 31, L - 1));
+        const int cnt = nl < 0 ? NT : nl;
+        if (p < L)
+        {
+            int il = 0;
+            for (int x = 0; x < cnt; ++x)
             {
-                int t = pt[2 * i + w];
-                if (t < 0) continue;
-                int p0 = alns[t].p0, n = alns[t].n;
-                if (p < p0 || p >= p0 + n) continue;
-                int64_t r = rec_off[t] + (p - p0);
-                uint8_t cd = rec.code[r];
-                int l = rec.inslen[r];
+                const int e = nl < 0 ? x : wlist[x];
+                const unsigned dd = (unsigned)(p - e_p0[e]);
+                if (dd >= (unsigned)e_n[e]) continue;
+                const int64_t r = e_roff[e] + dd;
+                const uint8_t cd = rec.code[r];
+                const int l = rec.inslen[r];
                 if (l > il) il = l;
                 if ((cd & 8u) && il < 1) il = 1;
             }
+            inslen[p] = il;
         }
-        inslen[p] = il;
+        __syncwarp();
     }
     __syncthreads();
     // ---- 3. view offsets: exclusive scan of inslen[p] + 1 ------------------------------------
@@ -176,85 +220,87 @@ __global__ void __launch_bounds__(K3_THREADS) k3_pileup_vote_kernel(
         for (int k = 1; k < 6; ++k) if (c[k] > mx) { idx = k; mx = c[k]; }
         double half = (double)cv / 2;
         double thr = __dmul_rn((d.min_cov < half) ? half : d.min_cov, qq);
-        if (!(c[idx] >= thr)) return gap ? 255 : base;
+        if (!(mx >= thr)) return gap ? 255 : base;
         if (idx < 5) { if (gap) ++n_ins; else if (base != idx) ++n_sub; return idx; }
         if (!fix) return gap ? 255 : base;
         if (!gap) ++n_del;
         return 255;
     };
-    for (int p = tid; p < L; p += K3_THREADS)
+    for (int base = 0; base < L; base += K3_THREADS)
     {
-        double m[6] = {0, 0, 0, 0, 0, 0};
-        double gap0 = 0.0;
-        unsigned cv = 0, noins = 0, runs = 0;
-        const int il = inslen[p];
-        for (int i = 0; i < P; ++i)
+        const int p = base + tid;
+        const int lo = base + warp * 32;
+        if (lo >= L) continue;                       // warp-uniform
+        const int nl = build_list(lo, min(lo + 31, L - 1));
+        const int cnt = nl < 0 ? NT : nl;
+        if (p < L)
         {
-            if (!proper[i]) continue;
-#pragma unroll
-            for (int w = 0; w < 2; ++w)
+            double m[6] = {0, 0, 0, 0, 0, 0};
+            double gap0 = 0.0;
+            unsigned cv = 0, noins = 0, runs = 0;
+            const int il = inslen[p];
+            for (int x = 0; x < cnt; ++x)
             {
-                int t = pt[2 * i + w];
-                if (t < 0) continue;
-                int p0 = alns[t].p0, n = alns[t].n;
-                if (p < p0 || p >= p0 + n) continue;
-                int64_t r = rec_off[t] + (p - p0);
-                uint8_t cd = rec.code[r];
-                double mq = (double)alns[t].mapq;
-                double gw = __dmul_rn(d.bq_mean, mq);
+                const int e = nl < 0 ? x : wlist[x];
+                const unsigned dd = (unsigned)(p - e_p0[e]);
+                if (dd >= (unsigned)e_n[e]) continue;
+                const int64_t r = e_roff[e] + dd;
+                const uint8_t cd = rec.code[r];
+                const double mq = (double)e_mapq[e];
+                const double gw = __dmul_rn(d.bq_mean, mq);
                 if (rec.inslen[r]) ++runs;
                 if (cd & 8u) { gap0 = __dadd_rn(gap0, gw); ++noins; }
-                int sym = cd & 7u;
-                double wgt = (sym < 5) ? __dmul_rn((double)rec.qual[r], mq) : gw;
-                m[sym] = __dadd_rn(m[sym], wgt);
+                const int sym = cd & 7u;
+                const double wgt = (sym < 5) ? __dmul_rn((double)rec.qual[r], mq) : gw;
+                // m[sym] += wgt without a dynamically indexed local array
+#pragma unroll
+                for (int q = 0; q < 6; ++q) if (q == sym) m[q] = __dadd_rn(m[q], wgt);
                 ++cv;
             }
-        }
-        const int col0 = voff[p];
-        const bool ins_in = (p > flank) && (p <= L - flank);
-        // inserted columns in front of p
-        for (int k = 0; k < il; ++k)
-        {
-            double c[6] = {0, 0, 0, 0, 0, gap0};
-            unsigned ck = (k == 0) ? noins : 0;   // ins_cov[k]; noins bookings count in column 0
-            if (runs)
+            const int col0 = voff[p];
+            const bool ins_in = (p > flank) && (p <= L - flank);
+            // inserted columns in front of p
+            for (int k = 0; k < il; ++k)
             {
-                for (int i = 0; i < P; ++i)
+                double c[6] = {0, 0, 0, 0, 0, gap0};
+                unsigned ck = (k == 0) ? noins : 0;   // ins_cov[k]; noins bookings count in column 0
+                if (runs)
                 {
-                    if (!proper[i]) continue;
-#pragma unroll
-                    for (int w = 0; w < 2; ++w)
+                    for (int x = 0; x < cnt; ++x)
                     {
-                        int t = pt[2 * i + w];
-                        if (t < 0) continue;
-                        int p0 = alns[t].p0, n = alns[t].n;
-                        if (p < p0 || p >= p0 + n) continue;
-                        int64_t r = rec_off[t] + (p - p0);
+                        const int e = nl < 0 ? x : wlist[x];
+                        const unsigned dd = (unsigned)(p - e_p0[e]);
+                        if (dd >= (unsigned)e_n[e]) continue;
+                        const int64_t r = e_roff[e] + dd;
                         if (rec.inslen[r] <= k) continue;
-                        int rid = plans[t].read_id, R = reads.len[rid], rc = alns[t].is_rc;
-                        int q = rec.insq[r] + k;
-                        int b = oriented_base(reads, rid, R, rc, q);
-                        int ql = read_quals[qual_off[rid] + (rc ? R - 1 - q : q)];
-                        c[b] = __dadd_rn(c[b], __dmul_rn((double)ql, (double)alns[t].mapq));
+                        const int t = e_task[e];
+                        const int rid = plans[t].read_id, R = reads.len[rid], rc = alns[t].is_rc;
+                        const int q = rec.insq[r] + k;
+                        const int b = oriented_base(reads, rid, R, rc, q);
+                        const int ql = read_quals[qual_off[rid] + (rc ? R - 1 - q : q)];
+                        const double wgt = __dmul_rn((double)ql, (double)e_mapq[e]);
+#pragma unroll
+                        for (int qx = 0; qx < 5; ++qx) if (qx == b) c[qx] = __dadd_rn(c[qx], wgt);
                         ++ck;
                     }
                 }
+                if (k >= 1) ck += noins;   // polishing.h:159-160
+                int col = col0 + k;
+#pragma unroll
+                for (int s = 0; s < 6; ++s) profile[(size_t)col * 6 + s] = c[s];
+                cov[col] = ck; isgap[col] = 1;
+                decision[col] = ins_in ? (uint8_t)vote(c, ck, 1, -1) : 255;
             }
-            if (k >= 1) ck += noins;   // polishing.h:159-160
-            int col = col0 + k;
+            {
+                int col = col0 + il;
 #pragma unroll
-            for (int s = 0; s < 6; ++s) profile[(size_t)col * 6 + s] = c[s];
-            cov[col] = ck; isgap[col] = 1;
-            decision[col] = ins_in ? (uint8_t)vote(c, ck, 1, -1) : 255;
+                for (int s = 0; s < 6; ++s) profile[(size_t)col * 6 + s] = m[s];
+                cov[col] = cv; isgap[col] = 0;
+                int bs = cons[p];
+                decision[col] = (p >= flank && p < L - flank) ? (uint8_t)vote(m, cv, 0, bs) : 255;
+            }
         }
-        {
-            int col = col0 + il;
-#pragma unroll
-            for (int s = 0; s < 6; ++s) profile[(size_t)col * 6 + s] = m[s];
-            cov[col] = cv; isgap[col] = 0;
-            int base = cons[p];
-            decision[col] = (p >= flank && p < L - flank) ? (uint8_t)vote(m, cv, 0, base) : 255;
-        }
+        __syncwarp();
     }
     {
         typedef cub::BlockReduce<long long, K3_THREADS> BR2;

@@ -15,22 +15,28 @@
 // Mapping: one block per job, thread T owns K5_RPL consecutive rows, block-wide wavefront over columns
 // (thread T works on column t-T at step t), bottom rows handed down through shared memory, one
 // __syncthreads per step. Sequences longer than K5_THREADS*K5_RPL rows run as successive row bands with
-// the band's bottom row kept in global memory. Trace: 4 bits per cell as in k1_trace.cuh.
+// the band's bottom row kept in global memory.
+// Per cell: 4 DADD (diag+sub, H+step, V+step, S+GO -- S+GO serves both the cell to the right and the cell
+// below) and 4 fp64 compares; the gap-step values travel with the gap lengths (looked up in a shared-memory
+// copy of the table when a length changes, i.e. off the S critical path).
+// Trace: 4 bits per cell as in k1_trace.cuh, one u16 per thread and step, stored anti-diagonal-major
+// (index = step * row_threads + thread) so that a warp's stores of one step are contiguous.
 #pragma once
 #include "common.cuh"
 
 namespace svp
 {
 constexpr int K5_THREADS = 512;
-constexpr int K5_RPL = 8;
+constexpr int K5_RPL = 4;
 constexpr int K5_BAND = K5_THREADS * K5_RPL;
+constexpr int K5_SG = 2048;   // gap-step table entries kept in shared memory
 
 struct FinalJob
 {
     const uint8_t *ref;   // H, length n (device)
     const uint8_t *seq;   // V, length m (device)
     int32_t n, m;
-    int64_t trace_off;    // u32 words: n * row_threads
+    int64_t trace_off;    // u16 units: (n + K5_THREADS) * row_threads
     int32_t row_threads;  // nbands * K5_THREADS
     int64_t bnd_off;      // per-column band boundary (n + 1 entries)
     int32_t valid;
@@ -50,67 +56,82 @@ struct K5Tables
 
 __global__ void __launch_bounds__(K5_THREADS) k5_final_kernel(const FinalJob *__restrict__ jobs, K5Tables tb,
                                                              double MM, double MX, double GO, double INF,
-                                                             uint32_t *__restrict__ trace, double *__restrict__ bndS,
+                                                             uint16_t *__restrict__ trace, double *__restrict__ bndS,
                                                              double *__restrict__ bndV, int32_t *__restrict__ bndVL,
                                                              FinalEnd *__restrict__ ends)
 {
     const FinalJob job = jobs[blockIdx.x];
     if (!job.valid) return;
     const int T = threadIdx.x, n = job.n, m = job.m;
-    __shared__ double shS[2][K5_THREADS], shV[2][K5_THREADS];
+    __shared__ double shS[2][K5_THREADS], shV[2][K5_THREADS], shVG[2][K5_THREADS];
     __shared__ int shVL[2][K5_THREADS];
-    uint32_t *tr = trace + job.trace_off;
+    __shared__ double sg[K5_SG];
+    for (int i = T; i < K5_SG; i += K5_THREADS) sg[i] = (i >= 1 && i <= tb.size) ? tb.gapstep[i] : 0.0;
+    __syncthreads();
+    auto G = [&](int len) -> double { return (len < K5_SG) ? sg[len] : __ldg(tb.gapstep + len); };
+    uint16_t *tr = trace + job.trace_off;
     double *bS = bndS + job.bnd_off, *bV = bndV + job.bnd_off;
     int32_t *bVL = bndVL + job.bnd_off;
     const int nbands = job.row_threads / K5_THREADS;
+    const double g1 = sg[1];
 
     for (int band = 0; band < nbands; ++band)
     {
         const int row0 = band * K5_BAND + T * K5_RPL;   // rows row0+1 .. row0+K5_RPL
-        double S[K5_RPL], H[K5_RPL];
+        double S[K5_RPL], SO[K5_RPL], H[K5_RPL], HG[K5_RPL];
         int HL[K5_RPL], sv[K5_RPL];
 #pragma unroll
         for (int k = 0; k < K5_RPL; ++k)
         {
             int row = row0 + k + 1;
             S[k] = (row <= m) ? tb.edge[row] : 0.0;
-            H[k] = INF; HL[k] = 1;
+            SO[k] = __dadd_rn(S[k], GO);
+            H[k] = INF; HL[k] = 1; HG[k] = g1;
             sv[k] = (row <= m) ? job.seq[row - 1] : 255;
         }
         double prev_up = (row0 <= m) ? tb.edge[row0] : 0.0;   // S[row0][0]
         const bool live = row0 < m;                            // this thread owns at least one real row
         const int nsteps = n + K5_THREADS - 1;
+        const size_t tcol = (size_t)band * K5_THREADS + T;
         for (int t = 0; t < nsteps; ++t)
         {
             const int col = t - T + 1;
             const int par = t & 1;
             if (col >= 1 && col <= n && live)
             {
-                double up_s, up_v; int up_vl;
+                double up_s, up_v, up_vg; int up_vl;
                 if (T == 0)
                 {
-                    if (band == 0) { up_s = tb.edge[col]; up_v = INF; up_vl = 1; }
-                    else { up_s = bS[col]; up_v = bV[col]; up_vl = bVL[col]; }
+                    if (band == 0) { up_s = tb.edge[col]; up_v = INF; up_vl = 1; up_vg = g1; }
+                    else { up_s = bS[col]; up_v = bV[col]; up_vl = bVL[col]; up_vg = G(up_vl); }
                 }
-                else { up_s = shS[par ^ 1][T - 1]; up_v = shV[par ^ 1][T - 1]; up_vl = shVL[par ^ 1][T - 1]; }
+                else
+                {
+                    up_s = shS[par ^ 1][T - 1]; up_v = shV[par ^ 1][T - 1]; up_vl = shVL[par ^ 1][T - 1];
+                    up_vg = shVG[par ^ 1][T - 1];
+                }
                 const int hc = job.ref[col - 1];
                 double diag = prev_up;
                 prev_up = up_s;
+                double up_so = __dadd_rn(up_s, GO);
                 uint32_t tw = 0;
 #pragma unroll
                 for (int k = 0; k < K5_RPL; ++k)
                 {
                     double inter = __dadd_rn(diag, (hc == sv[k]) ? MM : MX);
                     diag = S[k];
-                    double hext = __dadd_rn(H[k], __ldg(tb.gapstep + HL[k]));
-                    double hopn = __dadd_rn(S[k], GO);
+                    double hext = __dadd_rn(H[k], HG[k]);
+                    double hopn = SO[k];
                     uint32_t code;
                     double hh;
-                    if (hext < hopn) { hh = hopn; HL[k] = 1; code = 0u; } else { hh = hext; HL[k] += 1; code = 1u; }
+                    // the step value of a gap that gets extended is looked up before the compare resolves
+                    const double hg_ext = G(HL[k] + 1), vg_ext = G(up_vl + 1);
+                    if (hext < hopn) { hh = hopn; HL[k] = 1; HG[k] = g1; code = 0u; }
+                    else { hh = hext; HL[k] += 1; HG[k] = hg_ext; code = 1u; }
                     H[k] = hh;
-                    double vext = __dadd_rn(up_v, __ldg(tb.gapstep + up_vl));
-                    double vopn = __dadd_rn(up_s, GO);
-                    if (vext < vopn) { up_v = vopn; up_vl = 1; } else { up_v = vext; up_vl += 1; code |= 2u; }
+                    double vext = __dadd_rn(up_v, up_vg);
+                    if (vext < up_so) { up_v = up_so; up_vl = 1; up_vg = g1; }
+                    else { up_v = vext; up_vl += 1; up_vg = vg_ext; code |= 2u; }
                     double gap; uint32_t gsel;
                     if (up_v < hh) { gap = hh; gsel = 8u; } else { gap = up_v; gsel = 4u; }
                     double sn;
@@ -123,11 +144,13 @@ __global__ void __launch_bounds__(K5_THREADS) k5_final_kernel(const FinalJob *__
                         else if (hh == sn) code = (code & 3u) | 8u;
                     }
                     tw |= code << (4 * k);
-                    S[k] = sn; up_s = sn;
+                    S[k] = sn;
+                    up_so = __dadd_rn(sn, GO);
+                    SO[k] = up_so;
                 }
-                shS[par][T] = up_s; shV[par][T] = up_v; shVL[par][T] = up_vl;
-                if (T == K5_THREADS - 1 && band + 1 < nbands) { bS[col] = up_s; bV[col] = up_v; bVL[col] = up_vl; }
-                tr[(size_t)(col - 1) * job.row_threads + band * K5_THREADS + T] = tw;
+                shS[par][T] = S[K5_RPL - 1]; shV[par][T] = up_v; shVL[par][T] = up_vl; shVG[par][T] = up_vg;
+                if (T == K5_THREADS - 1 && band + 1 < nbands) { bS[col] = S[K5_RPL - 1]; bV[col] = up_v; bVL[col] = up_vl; }
+                tr[(size_t)t * job.row_threads + tcol] = (uint16_t)tw;
             }
             __syncthreads();
         }
@@ -144,23 +167,28 @@ struct CigarOut
     double score;
 };
 
-__global__ void k5_traceback_kernel(const FinalJob *__restrict__ jobs, int njobs, const uint32_t *__restrict__ trace,
-                                    const FinalEnd *__restrict__ ends, double INF, char *__restrict__ cig_op,
-                                    uint32_t *__restrict__ cig_cnt, int cap, CigarOut *__restrict__ out)
+// One warp per job. The path is followed in bulk: the 32 lanes read the next 32 cells along the current
+// direction (diagonal, or the row / column of a gap being extended), a ballot finds where the run ends, and
+// the whole run is emitted at once -- the number of dependent trace loads drops from one per path step to
+// about one per 32. All lanes carry the same (col, row, CIGAR) state; lane 0 writes.
+constexpr int K5TB_WARPS = 4;
+__global__ void __launch_bounds__(K5TB_WARPS * 32) k5_traceback_kernel(
+    const FinalJob *__restrict__ jobs, int njobs, const uint16_t *__restrict__ trace, const FinalEnd *__restrict__ ends,
+    double INF, char *__restrict__ cig_op, uint32_t *__restrict__ cig_cnt, int cap, CigarOut *__restrict__ out)
 {
-    int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.x * K5TB_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (j >= njobs) return;
     const FinalJob job = jobs[j];
     if (!job.valid) return;
     char *op = cig_op + (size_t)j * cap;
     uint32_t *cnt = cig_cnt + (size_t)j * cap;
-    const uint32_t *tr = trace + job.trace_off;
+    const uint16_t *tr = trace + job.trace_off;
     int ne = 0;          // elements emitted (reverse order)
     char last = 0; uint32_t run = 0;
     auto emit = [&](char c, uint32_t k) {
         if (k == 0) return;
         if (c == last) { run += k; return; }
-        if (run) { if (ne < cap) { op[ne] = last; cnt[ne] = run; } ++ne; }
+        if (run) { if (ne < cap && lane == 0) { op[ne] = last; cnt[ne] = run; } ++ne; }
         last = c; run = k;
     };
     CigarOut o;
@@ -175,40 +203,72 @@ __global__ void k5_traceback_kernel(const FinalJob *__restrict__ jobs, int njobs
     else
         o.score = ends[j].S;
     auto codeat = [&](int c, int r) -> uint32_t {
-        int slot = r - 1;
-        uint32_t w = tr[(size_t)(c - 1) * job.row_threads + (slot >> 3)];
-        return (w >> (4 * (slot & 7))) & 15u;
+        const int slot = r - 1, tg = slot / K5_RPL;
+        const int t = c - 1 + (tg % K5_THREADS);
+        uint32_t w = tr[(size_t)t * job.row_threads + tg];
+        return (w >> (4 * (slot % K5_RPL))) & 15u;
     };
+    const unsigned FULL = 0xffffffffu;
     while (col > 0 && row > 0)
     {
-        uint32_t code = codeat(col, row), sel = code >> 2;
-        if (sel == 0) { emit('M', 1); --col; --row; }
-        else if (sel == 1)
+        // ---- diagonal run ----
+        const bool in = (col - lane > 0) && (row - lane > 0);
+        const uint32_t c = in ? codeat(col - lane, row - lane) : 0xffu;
+        const unsigned stop = __ballot_sync(FULL, !in || (c >> 2) != 0);
+        const int nd = stop ? (__ffs(stop) - 1) : 32;
+        if (nd) { emit('M', (uint32_t)nd); col -= nd; row -= nd; }
+        if (nd == 32 || col <= 0 || row <= 0) continue;
+        uint32_t code = __shfl_sync(FULL, c, nd);   // the first non-diagonal cell, now at (col, row)
+        const uint32_t sel = code >> 2;
+        if (sel == 1)
         {
-            if (code & 2u)
-                while ((code & 2u) && row != 1) { --row; code = codeat(col, row); emit('I', 1); }
+            // vertical gap: while the cell says "extended" and row != 1 step up; then one more step
+            if ((code & 2u) && row != 1)
+            {
+                for (;;)
+                {
+                    const int r = row - 1 - lane;
+                    const uint32_t cc = (r >= 1) ? codeat(col, r) : 0u;
+                    // lane i holds the code read after i+1 steps; the walk stops there if it is not an extension or r == 1
+                    const unsigned st = __ballot_sync(FULL, r < 1 || !(cc & 2u) || r == 1);
+                    const int k = st ? __ffs(st) : 32;      // steps taken in this probe (1..32)
+                    emit('I', (uint32_t)k); row -= k;
+                    if (st) break;
+                }
+            }
             --row; emit('I', 1);
         }
         else
         {
-            if (code & 1u)
-                while ((code & 1u) && col != 1) { --col; code = codeat(col, row); emit('D', 1); }
+            if ((code & 1u) && col != 1)
+            {
+                for (;;)
+                {
+                    const int cl = col - 1 - lane;
+                    const uint32_t cc = (cl >= 1) ? codeat(cl, row) : 0u;
+                    const unsigned st = __ballot_sync(FULL, cl < 1 || !(cc & 1u) || cl == 1);
+                    const int k = st ? __ffs(st) : 32;
+                    emit('D', (uint32_t)k); col -= k;
+                    if (st) break;
+                }
+            }
             --col; emit('D', 1);
         }
     }
     emit('I', (uint32_t)row);
     emit('D', (uint32_t)col);
-    if (run) { if (ne < cap) { op[ne] = last; cnt[ne] = run; } ++ne; }
+    if (run) { if (ne < cap && lane == 0) { op[ne] = last; cnt[ne] = run; } ++ne; }
     o.n_cigar = ne;
     int st = ne < cap ? ne : cap;
     o.stored = st;
+    __syncwarp();
     // reverse the stored prefix in place (if truncated the caller only gets n_cigar right)
-    if (ne <= cap)
+    if (ne <= cap && lane == 0)
         for (int a = 0, b = ne - 1; a < b; ++a, --b)
         {
             char c = op[a]; op[a] = op[b]; op[b] = c;
             uint32_t x = cnt[a]; cnt[a] = cnt[b]; cnt[b] = x;
         }
-    out[j] = o;
+    if (lane == 0) out[j] = o;
 }
 }  // namespace svp
