@@ -46,8 +46,12 @@ struct TracePlan
     int32_t end_col;      // DP column of the end cell (0..L)
     int32_t c0;           // first window column (0-based) of the traced sub-matrix; DP column 0 == window col c0
     int32_t ncols;        // number of window columns traced (end_col - c0)
-    int64_t trace_off;    // word offset into the trace arena
+    int32_t band_w;       // >= 0: banded traced pass over the diagonals |(j - i) - (end_col - R)| <= band_w; -1: strip kernel
+    int32_t dlo;          // band: lowest diagonal j - i
+    int32_t pad_;
 };
+// traced-pass classes (plan_kernel bins tasks by band width)
+enum { TC_BAND16 = 0, TC_BAND32 = 1, TC_STRIP5 = 2, TC_STRIP8 = 3, TC_N = 4 };
 }  // namespace svp
 
 #define SVP_CHECK(call)                                                                              \

@@ -115,7 +115,7 @@ struct svp_ctx
     DevBuf read_quals, qual_off;            // qualities (bytes) per read, offsets
     DevBuf task_read, task_win, task_idx19, task_idx32;
     int ntasks = 0, n19 = 0, n32 = 0;
-    DevBuf score_out, plans, units, E, scan_tmp, trace, ops, alns;
+    DevBuf score_out, plans, units, E, tunits, TE, cls_count, cls_list, scan_tmp, trace, ops, alns;
     DevBuf rec_code, rec_qual, rec_inslen, rec_insq;
     int64_t E_total = 0;
     // ---- polish pipeline ----

@@ -13,15 +13,12 @@
 // (substitution score 0 keeps S == 0 there, which is exactly the free-begin row of
 // AlignConfig<true,false,false,true>), so the read's last row is always the last slot of lane 7.
 //
-// Per cell pair: 1 LDS (query profile), IMAD (diag + sub), 4x VIADDMNMX -- no trace, no compares:
-//   H'   = max(H + ge, So_left)            So := S + go of the cell to the left
-//   M    = max(H' + go, So_diag + sub)     = max(H', diag + sub) + go
-//   V    = max(V_up + ge, M_up)            == max(V_up + ge, So_up): the V_up + go term of So_up = max(M_up, V_up + go)
-//                                          never wins against V_up + ge because ge > go
-//   So   = max(V + go, M)
-// so the only loop-carried dependency down a lane's rows is ONE instruction per row (the V chain); everything
-// else of a column is independent work. (The textbook S = max3(diag+sub, H', V); So = S + go form needs one
-// instruction less on the ALU pipe but chains three dependent instructions per row, which left the pipe idle.)
+// Per cell pair: 1 LDS (query profile), IMAD (diag + sub), VIADDMNMX (H), VIADDMNMX (V), VIMNMX3 (S),
+// IMAD (S + go) -- no trace, no compares. Three of the six sit on the 16-lane ALU pipe, which is the bound.
+// The recurrence chains three dependent instructions down a lane's rows (V -> S -> S+go -> V of the next
+// row), so every step advances TWO window columns: cell (k, a) and cell (k-1, b = a+1) are independent, the
+// unrolled code interleaves the two chains, and per-step overhead (shuffles, range checks, window decode)
+// is paid once per column pair. A window of odd length gets one harmless extra column that is never scored.
 // Values are biased by +0x2000 so that both halves stay positive and plain 32-bit adds never carry between halves.
 #pragma once
 #include "common.cuh"
@@ -74,7 +71,7 @@ __global__ void __launch_bounds__(128) k1_score_kernel(const int32_t *__restrict
     const int pad = NSLOT - R;   // extra "row 0"s at the top
 
     constexpr uint32_t GE2 = 0xFFFFFFFFu;           // (-1,-1)
-    constexpr uint32_t GO2 = 0xFFFAFFFAu;           // (-6,-6), per-half addend of VIADDMNMX
+    constexpr uint32_t GO2 = 0u - 0x00060006u;      // 32-bit add of this subtracts 6 from both halves (no borrow)
     constexpr uint32_t NEG2 = 0x00010001u;          // "-infinity": biased 1
     constexpr uint32_t ROW0_SO = k1_pk(GAP_OPEN);   // S == 0 plus gap open
 
@@ -94,11 +91,9 @@ __global__ void __launch_bounds__(128) k1_score_kernel(const int32_t *__restrict
 #pragma unroll
         for (int c = 0; c < 5; ++c)
         {
-            // substitution scores of both strands as one 32-bit addend: sf + sr * 65536 (two's complement; the
-            // biased halves never borrow from each other)
-            int sf = (row < 1) ? 0 : ((c == rf) ? MATCH : MISMATCH);
-            int sr = (row < 1) ? 0 : ((c == rr) ? MATCH : MISMATCH);
-            prof[c * PST + k * G + g] = (uint32_t)(sf + sr * 65536);
+            uint32_t sf = (row < 1) ? 6u : ((c == rf) ? 7u : 2u);   // sub - go
+            uint32_t sr = (row < 1) ? 6u : ((c == rr) ? 7u : 2u);
+            prof[c * PST + k * G + g] = sf | (sr << 16);
         }
         int s0 = (row >= 1) ? -(5 + row) : 0;
         so[k] = k1_pk(s0 + GAP_OPEN);
@@ -110,57 +105,77 @@ __global__ void __launch_bounds__(128) k1_score_kernel(const int32_t *__restrict
         int sa = (rowa >= 1) ? -(5 + rowa) : 0;
         prev_up = (g == 0) ? ROW0_SO : k1_pk(sa + GAP_OPEN);
     }
-    uint32_t out_so = so[RPL - 1], out_v = NEG2;
+    uint32_t out_so0 = so[RPL - 1], out_v0 = NEG2, out_so1 = so[RPL - 1], out_v1 = NEG2;
     uint32_t best = so[RPL - 1];
     int colF = 0, colR = 0;
     uint32_t ww = 0, wn = 0;
     const uint32_t *w2p = wins.w2 + (size_t)wunit * 2;
     const uint32_t *wnp = wins.wn + (size_t)wunit;
 
-    const int nsteps = __reduce_max_sync(0xffffffffu, live ? L + G - 1 : 0);
+    const int nsteps = __reduce_max_sync(0xffffffffu, live ? (L + 1) / 2 + G - 1 : 0);
     for (int t = 0; t < nsteps; ++t)
     {
-        uint32_t r_so = __shfl_up_sync(0xffffffffu, out_so, 1, G);
-        uint32_t r_v = __shfl_up_sync(0xffffffffu, out_v, 1, G);
-        const int jj = t - g;
+        uint32_t r_so0 = __shfl_up_sync(0xffffffffu, out_so0, 1, G);
+        uint32_t r_v0 = __shfl_up_sync(0xffffffffu, out_v0, 1, G);
+        uint32_t r_so1 = __shfl_up_sync(0xffffffffu, out_so1, 1, G);
+        uint32_t r_v1 = __shfl_up_sync(0xffffffffu, out_v1, 1, G);
+        const int jj = 2 * (t - g);   // window columns jj (a) and jj + 1 (b)
         if (jj >= 0 && jj < L)
         {
-            if (g == 0) { r_so = ROW0_SO; r_v = NEG2; }
+            if (g == 0) { r_so0 = ROW0_SO; r_v0 = NEG2; r_so1 = ROW0_SO; r_v1 = NEG2; }
             if ((jj & 15) == 0)
             {
                 ww = __ldg(w2p + (jj >> 4));
                 if ((jj & 31) == 0) wn = __ldg(wnp + (jj >> 5));
             }
-            // consume one base: the packer stores 0 in the 2-bit plane under an N, so c = c2 + 4*n is 0..4
-            const int c = (int)(ww & 3u) + (int)((wn & 1u) << 2);
-            ww >>= 2; wn >>= 1;
-            const uint32_t *pr = prof + c * PST + g;
-            uint32_t diag = prev_up;
-            prev_up = r_so;
-            uint32_t up_v = __viaddmax_s16x2(r_v, GE2, r_so);   // first row of the lane: the neighbour's true So
-            uint32_t up_so = r_so;
+            // consume two bases: the packer stores 0 in the 2-bit plane under an N, so c = c2 + 4*n is 0..4
+            const int ca = (int)(ww & 3u) + (int)((wn & 1u) << 2);
+            const int cb = (int)((ww >> 2) & 3u) + (int)((wn & 2u) << 1);
+            ww >>= 4; wn >>= 2;
+            const uint32_t *pa = prof + ca * PST + g;
+            const uint32_t *pb = prof + cb * PST + g;
+            uint32_t dA = prev_up;        // So(row above, a - 1)
+            prev_up = r_so1;              // So(row above, b): the diagonal of the next step's column a
+            uint32_t dB = r_so0;          // So(row above, a)
+            uint32_t uA = r_so0, vA = r_v0, uB = r_so1, vB = r_v1;
 #pragma unroll
             for (int k = 0; k < RPL; ++k)
             {
-                const uint32_t interg = diag + pr[k * G];
-                diag = so[k];
-                h[k] = __viaddmax_s16x2(h[k], GE2, so[k]);
-                const uint32_t m = __viaddmax_s16x2(h[k], GO2, interg);
-                up_so = __viaddmax_s16x2(up_v, GO2, m);
-                so[k] = up_so;
-                if (k + 1 < RPL) up_v = __viaddmax_s16x2(up_v, GE2, m);
+                // column a
+                const uint32_t interA = dA + pa[k * G];
+                dA = so[k];
+                const uint32_t hA = __viaddmax_s16x2(h[k], GE2, so[k]);
+                vA = __viaddmax_s16x2(vA, GE2, uA);
+                uA = __vimax3_s16x2(interA, hA, vA) * one + GO2;   // IMAD with a runtime 1: keeps this add off the ALU pipe
+                // column b (its chain runs one row behind column a's)
+                const uint32_t interB = dB + pb[k * G];
+                dB = uA;
+                const uint32_t hB = __viaddmax_s16x2(hA, GE2, uA);
+                vB = __viaddmax_s16x2(vB, GE2, uB);
+                uB = __vimax3_s16x2(interB, hB, vB) * one + GO2;
+                h[k] = hB; so[k] = uB;
             }
-            out_so = up_so; out_v = up_v;
+            out_so0 = uA; out_v0 = vA; out_so1 = uB; out_v1 = vB;
             if (g == G - 1)
             {
                 // strict improvement only: the leftmost maximum wins (dp_scout.h:173). Improvements are rare
                 // (a handful per task), so the per-half bookkeeping sits behind a branch.
-                const uint32_t m = __vmaxs2(best, up_so);
+                uint32_t m = __vmaxs2(best, uA);
                 if (m != best)
                 {
-                    if ((up_so & 0xffffu) > (best & 0xffffu)) colF = jj + 1;   // halves are biased positive
-                    if ((up_so >> 16) > (best >> 16)) colR = jj + 1;
+                    if ((uA & 0xffffu) > (best & 0xffffu)) colF = jj + 1;   // halves are biased positive
+                    if ((uA >> 16) > (best >> 16)) colR = jj + 1;
                     best = m;
+                }
+                if (jj + 1 < L)
+                {
+                    m = __vmaxs2(best, uB);
+                    if (m != best)
+                    {
+                        if ((uB & 0xffffu) > (best & 0xffffu)) colF = jj + 2;
+                        if ((uB >> 16) > (best >> 16)) colR = jj + 2;
+                        best = m;
+                    }
                 }
             }
         }

@@ -21,27 +21,40 @@ constexpr int KT_WARPS = 4;
 constexpr int KT_NEG = INT32_MIN / 2;   // seqan/align/dp_cell.h:144-145
 
 // ---------------------------------------------------------------------------------------------
-// plan: strand choice (mapping.h:121), mapQ, and the traced column window.
-// Any alignment of the read ending in the last row at column e with score >= s spans at most
+// plan: strand choice (mapping.h:121), mapQ, and the part of the matrix the traced pass has to cover.
+//
+// Column window: any alignment of the read ending in the last row at column e with score >= s spans at most
 // R + max(0, R - s - 5) columns (m matches <= R, D deleted columns cost >= 5 + D), so the sub-matrix
 // starting at c0 = e - R - max(0, R - s) - 8 contains the reference's traceback path and every path
-// that ties with it at the end cell; cells on that path keep their values, hence all trace decisions
-// on the path are identical to the full matrix. full_window != 0 disables the restriction.
+// that ties with it at the end cell.
+// Diagonal band: a cell (i, j) lies on a path that ends in (R, e) with score >= s only if
+// |(e - j) - (R - i)| <= R - s - 5 (the path still has to absorb that many gap characters, costing at
+// least 5 + that many, and can collect at most R matches). Cells outside the band w = max(0, R - s) can be
+// replaced by -infinity: every cell ON a co-optimal path keeps its exact value (its optimal predecessor is
+// in the band), and a candidate that is lowered was strictly smaller than the winner already (had it tied,
+// it would itself be on a co-optimal path and therefore inside the band), so every trace decision the
+// traceback reads is identical to the full matrix. full_window != 0 disables both restrictions.
 // ---------------------------------------------------------------------------------------------
+constexpr int KB_MAXW16 = 15;   // 2w+1 <= 32 diagonals: 16 lanes x 2 diagonals
+constexpr int KB_MAXW32 = 31;   // 2w+1 <= 64 diagonals: 32 lanes x 2 diagonals
+
+__host__ __device__ inline int kb_row_words(int R) { return (R >> 3) + 1; }   // trace words per diagonal (rows 0..R)
+
 __global__ void plan_kernel(const int32_t *__restrict__ task_read, const int32_t *__restrict__ task_win, int ntasks,
                             const int32_t *__restrict__ read_len, const ScoreOut *__restrict__ sc,
                             const uint8_t *__restrict__ win_done, TracePlan *__restrict__ plan,
-                            int64_t *__restrict__ units, int full_window)
+                            int64_t *__restrict__ units, int64_t *__restrict__ tunits,
+                            int32_t *__restrict__ cls_count, int32_t *__restrict__ cls_list, int full_window)
 {
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= ntasks) return;
     ScoreOut o = sc[t];
     TracePlan p;
-    p.read_id = task_read[t]; p.win_id = task_win[t];
+    p.read_id = task_read[t]; p.win_id = task_win[t]; p.pad_ = 0;
     if (win_done && win_done[p.win_id])
     {
-        p.is_rc = 0; p.score = 0; p.end_col = 0; p.c0 = 0; p.ncols = -1; p.trace_off = 0;
-        plan[t] = p; units[t] = 0;
+        p.is_rc = 0; p.score = 0; p.end_col = 0; p.c0 = 0; p.ncols = -1; p.band_w = -1; p.dlo = 0;
+        plan[t] = p; units[t] = 0; tunits[t] = 0;
         return;
     }
     p.is_rc = !(o.score_f > o.score_r);
@@ -52,9 +65,23 @@ __global__ void plan_kernel(const int32_t *__restrict__ task_read, const int32_t
     int c0 = p.end_col - R - slack - 8;
     if (c0 < 0 || full_window) c0 = 0;
     p.c0 = c0; p.ncols = p.end_col - c0;
-    p.trace_off = 0;
+    int cls;
+    if (!full_window && slack <= KB_MAXW32)
+    {
+        p.band_w = slack; p.dlo = p.end_col - R - slack;
+        cls = slack <= KB_MAXW16 ? TC_BAND16 : TC_BAND32;
+        tunits[t] = (int64_t)(2 * slack + 2) * kb_row_words(R);
+    }
+    else
+    {
+        p.band_w = -1; p.dlo = 0;
+        cls = R <= 160 ? TC_STRIP5 : TC_STRIP8;
+        tunits[t] = (int64_t)(p.ncols > 0 ? p.ncols : 0) * 32;
+    }
     plan[t] = p;
-    units[t] = p.ncols + 2;   // trace columns / pileup records / (+ read length) path ops reserved for this task
+    units[t] = p.ncols + 2;   // pileup records / (+ read length) path ops reserved for this task
+    int at = atomicAdd(cls_count + cls, 1);
+    cls_list[(size_t)cls * ntasks + at] = t;
 }
 
 template <int RPL>
@@ -86,7 +113,7 @@ __global__ void __launch_bounds__(KT_WARPS * 32) k1_trace_kernel(const TracePlan
     const int R = reads.len[pl.read_id], runit = reads.off32[pl.read_id];
     const int wunit = wins.off32[pl.win_id];
     const int pad = NSLOT - R;
-    uint32_t *tr = trace + E[task] * 32;
+    uint32_t *tr = trace + E[task];   // E: word offsets of the trace arena
 
     int s[RPL], h[RPL];
 #pragma unroll
@@ -160,7 +187,122 @@ __global__ void __launch_bounds__(KT_WARPS * 32) k1_trace_kernel(const TracePlan
 }
 
 // ---------------------------------------------------------------------------------------------
-// K2: traceback (one thread per alignment) + the per-reference-position records the pileup consumes.
+// K1b: BANDED traced pass. LPA lanes per alignment (128 / LPA alignments per block), lane l owns the two
+// diagonals d = 2l, 2l+1 of the band (d = (j - i) - dlo). Step a covers the anti-diagonal i + j = a: every
+// lane computes the one cell of its diagonal with d == a - dlo (mod 2). Predecessors:
+//   diagonal (i-1, j-1): same diagonal, the lane's own previous value
+//   up       (i-1, j)  : diagonal d+1, computed one step earlier (own register, or lane l+1 via shuffle)
+//   left     (i, j-1)  : diagonal d-1, computed one step earlier (own register, or lane l-1 via shuffle)
+// Row 0 (S = 0, free begin) and DP column 0 (S = go + (i-1) ge) are "computed" as their initial values,
+// anything else outside the matrix or the band is -infinity.
+// Trace: 4 bits per cell as in the strip kernel; a lane collects the nibbles of 8 consecutive rows of one
+// diagonal into a word: trace[d * RW + (i >> 3)], RW = kb_row_words(R).
+// ---------------------------------------------------------------------------------------------
+constexpr int KB_THREADS = 128;
+constexpr int KB_RMAX = SVP_MAX_READ_LEN + 8;               // staged read bytes
+constexpr int KB_WMAX = SVP_MAX_READ_LEN + 2 * KB_MAXW32 + 8;   // staged window bytes (columns jbase .. e)
+constexpr int KB_SEQ_BYTES = KB_RMAX + KB_WMAX + 8;
+
+template <int LPA>
+__global__ void __launch_bounds__(KB_THREADS) k1_band_kernel(const TracePlan *__restrict__ plans, int ntasks,
+                                                            const int32_t *__restrict__ task_idx, SeqStore reads,
+                                                            SeqStore wins, const int64_t *__restrict__ TE,
+                                                            uint32_t *__restrict__ trace)
+{
+    constexpr int APB = KB_THREADS / LPA;   // alignments per block
+    __shared__ uint8_t kb_seq[APB][KB_SEQ_BYTES];
+    const int l = threadIdx.x % LPA, grp = threadIdx.x / LPA;
+    const int slot = blockIdx.x * APB + grp;
+    const unsigned gmask = (LPA == 32) ? 0xffffffffu : (0xffffu << (16 * ((threadIdx.x >> 4) & 1)));
+    const bool live = slot < ntasks;
+    int R = 0, e = 0, dlo = 0, B = 0, rc = 0, runit = 0, wunit = 0, jbase = 0;
+    uint32_t *tr = trace;
+    if (live)
+    {
+        const int task = task_idx[slot];
+        const TracePlan pl = plans[task];
+        R = reads.len[pl.read_id]; runit = reads.off32[pl.read_id];
+        wunit = wins.off32[pl.win_id];
+        e = pl.end_col; dlo = pl.dlo; B = 2 * pl.band_w + 1; rc = pl.is_rc;
+        tr = trace + TE[task];
+        jbase = dlo > 0 ? dlo : 0;   // window columns jbase+1 .. e are staged at sW[j - jbase]
+    }
+    uint8_t *sR = kb_seq[grp], *sW = kb_seq[grp] + KB_RMAX;
+    for (int i = l; i < R; i += LPA)
+    {
+        int b;
+        if (rc) { b = seq_base(reads, runit, R - 1 - i); b = (b < 4) ? 3 - b : 4; }
+        else b = seq_base(reads, runit, i);
+        sR[i + 1] = (uint8_t)b;                       // sR[row], rows 1..R
+    }
+    for (int j = jbase + 1 + l; j <= e; j += LPA) sW[j - jbase] = (uint8_t)seq_base(wins, wunit, j - 1);
+    __syncwarp(gmask);
+
+    // own diagonals: slot 0 = 2l, slot 1 = 2l + 1; values of the last cell computed on each
+    int S0 = KT_NEG, H0 = KT_NEG, V0 = KT_NEG, S1 = KT_NEG, H1 = KT_NEG, V1 = KT_NEG;
+    uint32_t acc0 = 0, acc1 = 0;
+    const int RW = kb_row_words(R);
+    // first step: the smallest anti-diagonal with a cell in the matrix, rounded down to even parity (slot 0)
+    int a_first = jbase;
+    if ((a_first - dlo) & 1) --a_first;
+    const int a_last = R + e;
+    const int d0 = 2 * l, d1 = 2 * l + 1;
+
+    auto cell = [&](int a, int d, int diagS, int upS, int upV, int leftS, int leftH, int &S, int &H, int &V,
+                    uint32_t &acc) {
+        const int i = (a - dlo - d) >> 1, j = a - i;
+        const bool inside = (d < B) && (i >= 0) && (i <= R) && (j >= 0) && (j <= e);
+        if (!inside) { S = KT_NEG; H = KT_NEG; V = KT_NEG; return; }
+        if (i == 0) { S = 0; H = KT_NEG; V = KT_NEG; return; }                 // free first row
+        if (j == 0) { S = -(5 + i); H = KT_NEG; V = KT_NEG; return; }          // initial column (dp_formula_affine.h:291-325)
+        const int sub = (sR[i] == sW[j - jbase]) ? MATCH : MISMATCH;
+        const int inter = diagS + sub;
+        const int hext = leftH + GAP_EXT, hopn = leftS + GAP_OPEN;
+        uint32_t code = (hext < hopn) ? 0u : 1u;             // tie -> extension
+        const int hh = max(hext, hopn);
+        const int vext = upV + GAP_EXT, vopn = upS + GAP_OPEN;
+        code |= (vext < vopn) ? 0u : 2u;
+        const int vv = max(vext, vopn);
+        const int gap = max(vv, hh);
+        const uint32_t gsel = (vv < hh) ? 8u : 4u;           // tie -> vertical
+        const int sn = max(inter, gap);
+        if (inter < gap) code |= gsel;                       // tie -> diagonal
+        if (i == R && j == e)
+        {
+            // end-cell correction (dp_algorithm_impl.h:1170-1185)
+            if (vv == sn) code = (code & 3u) | 4u;
+            else if (hh == sn) code = (code & 3u) | 8u;
+        }
+        S = sn; H = hh; V = vv;
+        acc |= code << (4 * (i & 7));
+        if ((i & 7) == 7 || i == R || j == e) { tr[(size_t)d * RW + (i >> 3)] = acc; acc = 0; }
+    };
+
+    const int nsteps = __reduce_max_sync(0xffffffffu, live ? (a_last - a_first + 2) / 2 : 0);   // step pairs
+    int a = a_first;
+    for (int it = 0; it < nsteps; ++it, a += 2)
+    {
+        // even-parity step: slot 0. left neighbour = lane l-1's slot 1, up neighbour = own slot 1
+        int lS = __shfl_up_sync(0xffffffffu, S1, 1, LPA);
+        int lH = __shfl_up_sync(0xffffffffu, H1, 1, LPA);
+        if (l == 0) { lS = KT_NEG; lH = KT_NEG; }
+        {
+            const int diagS = S0;
+            cell(a, d0, diagS, S1, V1, lS, lH, S0, H0, V0, acc0);
+        }
+        // odd-parity step: slot 1. up neighbour = lane l+1's slot 0, left neighbour = own slot 0
+        int uS = __shfl_down_sync(0xffffffffu, S0, 1, LPA);
+        int uV = __shfl_down_sync(0xffffffffu, V0, 1, LPA);
+        if (l == LPA - 1) { uS = KT_NEG; uV = KT_NEG; }
+        {
+            const int diagS = S1;
+            cell(a + 1, d1, diagS, uS, uV, S0, H0, S1, H1, V1, acc1);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K2: traceback (one WARP per alignment) + the per-reference-position records the pileup consumes.
 // Literal restatement of add_read_to_profile's bookkeeping (include/sviper/polishing.h:54-107) on the
 // view columns of the alignment; see oracle/oracle_polish.c:orc_add_read for the same logic on the CPU.
 // ---------------------------------------------------------------------------------------------
@@ -184,75 +326,105 @@ struct RecArrays
     uint16_t *insq;    // oriented read index of the first inserted base
 };
 
-template <int RPL>
-__device__ __forceinline__ uint32_t kt_code(const uint32_t *tr, int pad, int col, int row)
-{
-    int slot = pad + row - 1;
-    uint32_t w = tr[(size_t)(col - 1) * 32 + slot / RPL];
-    return (w >> (4 * (slot % RPL))) & 15u;
-}
+// One warp per alignment, both trace layouts (band: k1_band_kernel, strip: k1_trace_kernel<5|8>).
+// Phase A follows the path in bulk: the 32 lanes read the next 32 cells along the current direction
+// (diagonal, or the row / column of a gap being extended), a ballot finds where the run ends and the whole
+// run is emitted at once, so the number of dependent trace loads is ~ the number of path segments, not
+// the path length. All lanes carry the same (col, row, np) state.
+// Phase B builds the pileup records for 32 view columns at a time from ballots / prefix popcounts; it
+// is the data-parallel form of the sequential bookkeeping in add_read_to_profile (see the comments there).
+constexpr int K2_WARPS = 4;
 
-template <int RPL>
-__global__ void k2_traceback_kernel(const TracePlan *__restrict__ plans, int ntasks,
-                                    const int32_t *__restrict__ task_idx, SeqStore reads, SeqStore wins,
-                                    const uint8_t *__restrict__ read_quals, const int64_t *__restrict__ qual_off,
-                                    const uint32_t *__restrict__ trace, uint8_t *__restrict__ ops_buf,
-                                    RecArrays rec, const int64_t *__restrict__ E, AlnOut *__restrict__ out)
+__global__ void __launch_bounds__(K2_WARPS * 32) k2_traceback_kernel(
+    const TracePlan *__restrict__ plans, int ntasks, SeqStore reads, SeqStore wins,
+    const uint8_t *__restrict__ read_quals, const int64_t *__restrict__ qual_off,
+    const uint32_t *__restrict__ trace, uint8_t *__restrict__ ops_buf, RecArrays rec,
+    const int64_t *__restrict__ E, const int64_t *__restrict__ TE, AlnOut *__restrict__ out)
 {
-    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int t = blockIdx.x * K2_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (t >= ntasks) return;
-    if (task_idx) t = task_idx[t];
     const TracePlan pl = plans[t];
     if (pl.ncols < 0) return;   // window already converged
+    const unsigned FULL = 0xffffffffu;
     const int R = reads.len[pl.read_id], L = wins.len[pl.win_id];
-    const int pad = 32 * RPL - R;
-    const uint32_t *tr = trace + E[t] * 32;
+    const uint32_t *tr = trace + TE[t];
+    const int RW = kb_row_words(R);
+    const int band = pl.band_w >= 0;
+    const int rpl = (R <= 160) ? 5 : 8;            // strip layout: rows per lane (plan_kernel's class rule)
+    const int spad = 32 * rpl - R - 1;
+    int bad_cell = 0;
+    // trace nibble of the cell in local column col (DP column c0 + col), row
+    auto codeat = [&](int col, int row) -> uint32_t {
+        if (band)
+        {
+            const int d = pl.c0 + col - row - pl.dlo;
+            if (d < 0 || d > 2 * pl.band_w) return 0x100u;   // outside the band: stops every probe (checked below)
+            return (__ldg(tr + (size_t)d * RW + (row >> 3)) >> (4 * (row & 7))) & 15u;
+        }
+        const int slot = spad + row;
+        const int sl = (rpl == 5) ? slot / 5 : slot >> 3, sk = (rpl == 5) ? slot % 5 : slot & 7;
+        return (__ldg(tr + (size_t)(col - 1) * 32 + sl) >> (4 * sk)) & 15u;
+    };
     uint8_t *ops = ops_buf + E[t] + (int64_t)t * SVP_MAX_READ_LEN;      // cap: ncols + 2 + max read length
-    const int64_t ops_cap = E[t + 1] - E[t] + SVP_MAX_READ_LEN;
+    const int ops_cap = (int)(E[t + 1] - E[t]) + SVP_MAX_READ_LEN;
     AlnOut o;
     o.err = 0; o.is_rc = pl.is_rc; o.mapq = pl.score > 0 ? pl.score : 0;
 
+    // ---- phase A: traceback (dp_traceback_impl.h:391-420, :243-259, :321-336) -----------------
     int col = pl.ncols, row = R, np = 0, path_tail_d = 0;
     bool only_d = true;
+    auto emit = [&](char ch, int k) {   // k <= 32 ops of the same kind
+        if (lane < k && np + lane < ops_cap) ops[np + lane] = (uint8_t)ch;
+        np += k;
+    };
     while (col > 0 && row > 0)
     {
-        uint32_t code = kt_code<RPL>(tr, pad, col, row);
-        uint32_t sel = code >> 2;
-        if (sel == 0)
-        {
-            if (np < ops_cap) ops[np] = 'M'; ++np; --col; --row; only_d = false;
-        }
-        else if (sel == 1)
+        const bool in = (col - lane > 0) && (row - lane > 0);
+        const uint32_t c = in ? codeat(col - lane, row - lane) : 0xffu;
+        const unsigned stop = __ballot_sync(FULL, !in || (c >> 2) != 0);
+        const int nd = stop ? (__ffs(stop) - 1) : 32;
+        if (nd) { emit('M', nd); col -= nd; row -= nd; only_d = false; }
+        if (nd == 32 || col <= 0 || row <= 0) continue;
+        const uint32_t code = __shfl_sync(FULL, c, nd);   // first non-diagonal cell, now at (col, row)
+        if (code == 0x100u) { bad_cell = 1; break; }         // must not happen: the path left the band
+        if ((code >> 2) == 1)
         {
             only_d = false;
-            if (code & 2u)
+            if ((code & 2u) && row != 1)
             {
-                while ((code & 2u) && row != 1)
+                for (;;)
                 {
-                    --row; code = kt_code<RPL>(tr, pad, col, row);
-                    if (np < ops_cap) ops[np] = 'I'; ++np;
+                    const int r = row - 1 - lane;
+                    const uint32_t cc = (r >= 1) ? codeat(col, r) : 0u;
+                    const unsigned st = __ballot_sync(FULL, r < 1 || !(cc & 2u) || r == 1);
+                    const int k = st ? __ffs(st) : 32;
+                    emit('I', k); row -= k;
+                    if (st) break;
                 }
             }
-            --row;
-            if (np < ops_cap) ops[np] = 'I'; ++np;
+            --row; emit('I', 1);
         }
         else
         {
-            if (code & 1u)
+            int nD = 0;
+            if ((code & 1u) && col != 1)
             {
-                while ((code & 1u) && col != 1)
+                for (;;)
                 {
-                    --col; code = kt_code<RPL>(tr, pad, col, row);
-                    if (np < ops_cap) ops[np] = 'D'; ++np;
-                    if (only_d) ++path_tail_d;
+                    const int cl = col - 1 - lane;
+                    const uint32_t cc = (cl >= 1) ? codeat(cl, row) : 0u;
+                    const unsigned st = __ballot_sync(FULL, cl < 1 || !(cc & 1u) || cl == 1);
+                    const int k = st ? __ffs(st) : 32;
+                    emit('D', k); col -= k; nD += k;
+                    if (st) break;
                 }
             }
-            --col;
-            if (np < ops_cap) ops[np] = 'D'; ++np;
-            if (only_d) ++path_tail_d;
+            --col; emit('D', 1); ++nD;
+            if (only_d) path_tail_d += nD;
         }
     }
     if (np > ops_cap) o.err = 3;
+    if (bad_cell) o.err = 4;
     if (row > 0 && pl.c0 > 0) o.err = 1;   // must not happen: the window restriction was too tight
     const int lead_d = (row == 0) ? pl.c0 + col : 0;
     const int lead_i = row;
@@ -262,64 +434,89 @@ __global__ void k2_traceback_kernel(const TracePlan *__restrict__ plans, int nta
     o.npath = np; o.lead_i = lead_i;
     o.lead = lead_d;
     o.endpos = nops - (tail_d + path_tail_d);
+    __syncwarp();
     // trailing 'I's of the ref row: only when nothing follows the path
     int trail_i = 0;
-    if (tail_d == 0) { while (trail_i < np && ops[trail_i] == 'I') ++trail_i; if (trail_i == np) trail_i += lead_i; }
+    if (tail_d == 0 && o.err == 0)
+    {
+        for (int base = 0; base < np; base += 32)
+        {
+            const int x = base + lane;
+            const unsigned notI = __ballot_sync(FULL, x >= np || __ldcg(ops + x) != 'I');
+            if (notI) { trail_i += __ffs(notI) - 1; break; }
+            trail_i += 32;
+        }
+        if (trail_i > np) trail_i = np;
+        if (trail_i == np) trail_i += lead_i;
+    }
     const int ref_end = nops - trail_i;
 
+    // ---- phase B: pileup records (polishing.h:54-107) -----------------------------------------
+    // The reference walks the view columns [begin, end) sequentially; a run of consensus gaps ('I') is consumed
+    // together with the column that follows it (even when that column is `end` itself), every other column
+    // yields one record. Per record: the symbol, the length of the insertion run in front of it and the read
+    // index where that run starts, and the "no insertion after this base" flag of the else-branch (:88-95).
     if (rec.code != nullptr && o.err == 0)
     {
-        // forward pass over the view columns [begin, end)
         const int64_t ro = E[t];
-        const int64_t rcap = E[t + 1] - ro;
+        const int rcap = (int)(E[t + 1] - ro);
         const int runit = reads.off32[pl.read_id];
         const uint8_t *rq = read_quals + qual_off[pl.read_id];
         auto opat = [&](int idx) -> int {
             if (idx < lead) return (lead_i > 0) ? 'I' : 'D';
-            if (idx < lead + np) return ops[np - 1 - (idx - lead)];
+            if (idx < lead + np) return __ldcg(ops + (np - 1 - (idx - lead)));
             return 'D';
-        };
-        auto refgap = [&](int idx) -> bool {
-            if (idx < nops) return opat(idx) == 'I';
-            return opat(nops - 1) != 'I';   // seqan isGap() at position == length (gaps_array.h:749-783)
         };
         const int begin = lead;   // max(leading ref gaps, leading read gaps): one of them is zero
         const int end = (ref_end < o.endpos) ? ref_end : o.endpos;
-        int p = lead_d, q = lead_i;
-        o.p0 = p;
-        int i = 0;
-        for (int idx = begin; idx < end; ++idx)
+        int i_carry = 0, q_carry = 0, run_carry = 0, n_rec = 0, over = 0;
+        for (int base = begin; base <= end; base += 32)
         {
-            uint32_t cd = 0x80u;
-            uint16_t il = 0, iq = 0;
-            if (opat(idx) == 'I')
+            const int c = base + lane;
+            const bool valid = c <= end;
+            const int op = valid ? opat(c) : 'M';
+            const bool nextI = valid && (c + 1 < nops) && opat(c + 1) == 'I';
+            const bool isI = valid && op == 'I', isD = valid && op == 'D';
+            const unsigned mV = __ballot_sync(FULL, valid), mI = __ballot_sync(FULL, isI), mD = __ballot_sync(FULL, isD);
+            const unsigned below = (1u << lane) - 1u;
+            const int i_rec = i_carry + __popc(mV & ~mI & below);
+            const int qc = q_carry + __popc(mV & ~mD & below);
+            const unsigned x = ~mI & below;                      // non-'I' columns below this lane
+            const int il = x ? (lane - 1 - (31 - __clz(x))) : (lane + run_carry);
+            const bool emitrec = valid && !isI && (c < end || il > 0);
+            if (emitrec)
             {
-                iq = (uint16_t)q;
-                while (refgap(idx)) { ++il; ++q; ++idx; }
+                uint32_t cd = 0x80u;
+                if (il == 0 && c + 1 < nops && !nextI) cd |= 8u;
+                uint8_t qual = 0;
+                if (!isD)
+                {
+                    const int q = lead_i + qc;
+                    const int src = pl.is_rc ? (R - 1 - q) : q;
+                    int b = seq_base(reads, runit, src);
+                    if (pl.is_rc) b = (b < 4) ? 3 - b : 4;
+                    cd |= (uint32_t)b; qual = rq[src];
+                }
+                else
+                    cd |= 5u;
+                if (i_rec < rcap)
+                {
+                    rec.code[ro + i_rec] = (uint8_t)cd; rec.qual[ro + i_rec] = qual;
+                    rec.inslen[ro + i_rec] = (uint16_t)il;
+                    rec.insq[ro + i_rec] = (uint16_t)(il > 0 ? lead_i + qc - il : 0);
+                }
+                else
+                    over = 1;
             }
-            else if (!refgap(idx + 1))
-                cd |= 8u;
-            uint8_t qual = 0;
-            if (opat(idx) != 'D')
-            {
-                int src = pl.is_rc ? (R - 1 - q) : q;
-                int b = seq_base(reads, runit, src);
-                if (pl.is_rc) b = (b < 4) ? 3 - b : 4;
-                cd |= (uint32_t)b; qual = rq[src]; ++q;
-            }
-            else
-                cd |= 5u;
-            if (i < rcap)
-            {
-                rec.code[ro + i] = (uint8_t)cd; rec.qual[ro + i] = qual;
-                rec.inslen[ro + i] = il; rec.insq[ro + i] = iq;
-            }
-            ++i; ++p;
+            n_rec += __popc(__ballot_sync(FULL, emitrec));
+            i_carry += __popc(mV & ~mI);
+            q_carry += __popc(mV & ~mD);
+            run_carry = (mI == FULL) ? run_carry + 32 : __clz(~mI);
         }
-        if (i > rcap) o.err = 2;
-        o.n = i;
+        if (__any_sync(FULL, over)) o.err = 2;
+        o.p0 = lead_d; o.n = n_rec;
     }
     else { o.p0 = 0; o.n = 0; }
-    out[t] = o;
+    if (lane == 0) out[t] = o;
 }
 }  // namespace svp
