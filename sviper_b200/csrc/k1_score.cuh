@@ -35,9 +35,14 @@ template <int RPL>
 struct K1Shape
 {
     static constexpr int NSLOT = K1_G * RPL;
-    static constexpr int PST = (NSLOT + 31) & ~31;     // words per profile row (one window character)
-    static constexpr int TASK_WORDS = 5 * PST + 8;     // +8: successive groups land on different banks
+    // a lane's RPL profile entries of one window character are contiguous (fetched with LDS.128); the lane
+    // stride KPAD is a multiple of 4 words with KPAD/4 odd, so the 8 lanes of a task (= one quarter-warp, the
+    // conflict granularity of 128-bit loads) hit 8 distinct bank groups
+    static constexpr int KPAD = ((RPL + 3) / 4 * 4) + ((((RPL + 3) / 4) & 1) ? 0 : 4);
+    static constexpr int PST = K1_G * KPAD;            // words per profile row (one window character); multiple of 32
+    static constexpr int TASK_WORDS = 5 * PST + 8;
     static constexpr int SMEM_BYTES = K1_TASKS_PER_BLOCK * TASK_WORDS * 4;
+    static_assert(PST % 32 == 0 && TASK_WORDS % 4 == 0, "profile rows must keep bank phase and 16-byte alignment");
 };
 
 template <int RPL>
@@ -49,11 +54,11 @@ __global__ void __launch_bounds__(128) k1_score_kernel(const int32_t *__restrict
                                                        uint32_t one /* always 1; opaque to the compiler */)
 {
     using Sh = K1Shape<RPL>;
-    constexpr int G = K1_G, NSLOT = Sh::NSLOT, PST = Sh::PST;
+    constexpr int G = K1_G, NSLOT = Sh::NSLOT, PST = Sh::PST, KPAD = Sh::KPAD, NQ = (RPL + 3) / 4;
     extern __shared__ uint32_t k1_smem[];
     const int g = threadIdx.x & (G - 1), grp = threadIdx.x >> 3;
     const int slot = blockIdx.x * K1_TASKS_PER_BLOCK + grp;
-    uint32_t *prof = k1_smem + grp * Sh::TASK_WORDS;   // prof[c][k][g]
+    uint32_t *prof = k1_smem + grp * Sh::TASK_WORDS;   // prof[c][g][k]
 
     int R = 0, L = 0, runit = 0, wunit = 0, task = -1;
     if (slot < ntasks)
@@ -93,7 +98,7 @@ __global__ void __launch_bounds__(128) k1_score_kernel(const int32_t *__restrict
         {
             uint32_t sf = (row < 1) ? 6u : ((c == rf) ? 7u : 2u);   // sub - go
             uint32_t sr = (row < 1) ? 6u : ((c == rr) ? 7u : 2u);
-            prof[c * PST + k * G + g] = sf | (sr << 16);
+            prof[c * PST + g * KPAD + k] = sf | (sr << 16);
         }
         int s0 = (row >= 1) ? -(5 + row) : 0;
         so[k] = k1_pk(s0 + GAP_OPEN);
@@ -132,8 +137,18 @@ __global__ void __launch_bounds__(128) k1_score_kernel(const int32_t *__restrict
             const int ca = (int)(ww & 3u) + (int)((wn & 1u) << 2);
             const int cb = (int)((ww >> 2) & 3u) + (int)((wn & 2u) << 1);
             ww >>= 4; wn >>= 2;
-            const uint32_t *pa = prof + ca * PST + g;
-            const uint32_t *pb = prof + cb * PST + g;
+            uint32_t pa[NQ * 4], pb[NQ * 4];
+            {
+                const uint4 *qa = reinterpret_cast<const uint4 *>(prof + ca * PST + g * KPAD);
+                const uint4 *qb = reinterpret_cast<const uint4 *>(prof + cb * PST + g * KPAD);
+#pragma unroll
+                for (int q = 0; q < NQ; ++q)
+                {
+                    const uint4 x = qa[q], y = qb[q];
+                    pa[4 * q] = x.x; pa[4 * q + 1] = x.y; pa[4 * q + 2] = x.z; pa[4 * q + 3] = x.w;
+                    pb[4 * q] = y.x; pb[4 * q + 1] = y.y; pb[4 * q + 2] = y.z; pb[4 * q + 3] = y.w;
+                }
+            }
             uint32_t dA = prev_up;        // So(row above, a - 1)
             prev_up = r_so1;              // So(row above, b): the diagonal of the next step's column a
             uint32_t dB = r_so0;          // So(row above, a)
@@ -142,13 +157,13 @@ __global__ void __launch_bounds__(128) k1_score_kernel(const int32_t *__restrict
             for (int k = 0; k < RPL; ++k)
             {
                 // column a
-                const uint32_t interA = dA + pa[k * G];
+                const uint32_t interA = dA + pa[k];
                 dA = so[k];
                 const uint32_t hA = __viaddmax_s16x2(h[k], GE2, so[k]);
                 vA = __viaddmax_s16x2(vA, GE2, uA);
                 uA = __vimax3_s16x2(interA, hA, vA) * one + GO2;   // IMAD with a runtime 1: keeps this add off the ALU pipe
                 // column b (its chain runs one row behind column a's)
-                const uint32_t interB = dB + pb[k * G];
+                const uint32_t interB = dB + pb[k];
                 dB = uA;
                 const uint32_t hB = __viaddmax_s16x2(hA, GE2, uA);
                 vB = __viaddmax_s16x2(vB, GE2, uB);

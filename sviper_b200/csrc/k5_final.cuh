@@ -29,7 +29,6 @@ namespace svp
 constexpr int K5_THREADS = 512;
 constexpr int K5_RPL = 4;
 constexpr int K5_BAND = K5_THREADS * K5_RPL;
-constexpr int K5_SG = 2048;   // gap-step table entries kept in shared memory
 
 struct FinalJob
 {
@@ -54,6 +53,9 @@ struct K5Tables
     int32_t size;
 };
 
+// SMEM_TABLE: the whole gap-step table (tb.size + 1 doubles) sits in dynamic shared memory; otherwise it is
+// read through the read-only cache (only for tables beyond ~190 KB, i.e. sequences longer than ~24,000).
+template <bool SMEM_TABLE>
 __global__ void __launch_bounds__(K5_THREADS) k5_final_kernel(const FinalJob *__restrict__ jobs, K5Tables tb,
                                                              double MM, double MX, double GO, double INF,
                                                              uint16_t *__restrict__ trace, double *__restrict__ bndS,
@@ -65,15 +67,18 @@ __global__ void __launch_bounds__(K5_THREADS) k5_final_kernel(const FinalJob *__
     const int T = threadIdx.x, n = job.n, m = job.m;
     __shared__ double shS[2][K5_THREADS], shV[2][K5_THREADS], shVG[2][K5_THREADS];
     __shared__ int shVL[2][K5_THREADS];
-    __shared__ double sg[K5_SG];
-    for (int i = T; i < K5_SG; i += K5_THREADS) sg[i] = (i >= 1 && i <= tb.size) ? tb.gapstep[i] : 0.0;
-    __syncthreads();
-    auto G = [&](int len) -> double { return (len < K5_SG) ? sg[len] : __ldg(tb.gapstep + len); };
+    extern __shared__ double k5_sg[];
+    if (SMEM_TABLE)
+    {
+        for (int i = T; i <= tb.size; i += K5_THREADS) k5_sg[i] = tb.gapstep[i];
+        __syncthreads();
+    }
+    auto G = [&](int len) -> double { return SMEM_TABLE ? k5_sg[len] : __ldg(tb.gapstep + len); };
     uint16_t *tr = trace + job.trace_off;
     double *bS = bndS + job.bnd_off, *bV = bndV + job.bnd_off;
     int32_t *bVL = bndVL + job.bnd_off;
     const int nbands = job.row_threads / K5_THREADS;
-    const double g1 = sg[1];
+    const double g1 = tb.gapstep[1];
 
     for (int band = 0; band < nbands; ++band)
     {
@@ -91,6 +96,7 @@ __global__ void __launch_bounds__(K5_THREADS) k5_final_kernel(const FinalJob *__
         }
         double prev_up = (row0 <= m) ? tb.edge[row0] : 0.0;   // S[row0][0]
         const bool live = row0 < m;                            // this thread owns at least one real row
+        const int endk = m - 1 - row0;                         // slot of the last row, if this thread owns it
         const int nsteps = n + K5_THREADS - 1;
         const size_t tcol = (size_t)band * K5_THREADS + T;
         for (int t = 0; t < nsteps; ++t)
@@ -111,6 +117,7 @@ __global__ void __launch_bounds__(K5_THREADS) k5_final_kernel(const FinalJob *__
                     up_vg = shVG[par ^ 1][T - 1];
                 }
                 const int hc = job.ref[col - 1];
+                const bool endcol = (col == n);
                 double diag = prev_up;
                 prev_up = up_s;
                 double up_so = __dadd_rn(up_s, GO);
@@ -136,7 +143,7 @@ __global__ void __launch_bounds__(K5_THREADS) k5_final_kernel(const FinalJob *__
                     if (up_v < hh) { gap = hh; gsel = 8u; } else { gap = up_v; gsel = 4u; }
                     double sn;
                     if (inter < gap) { sn = gap; code |= gsel; } else sn = inter;
-                    if (col == n && row0 + k + 1 == m)
+                    if (endcol && k == endk)
                     {
                         FinalEnd e; e.S = sn; e.H = hh; e.V = up_v;
                         ends[blockIdx.x] = e;
