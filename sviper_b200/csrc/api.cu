@@ -102,6 +102,7 @@ int svp_align_batch(svp_ctx *ctx, const svp_align_in *in, svp_align_out *out, in
     if (rc) return rc;
     rc = upload_tasks(ctx, in->n_tasks, in->task_read, in->task_win, rlen.data());
     if (rc) return rc;
+    ctx->win_bytes = ctx->wins.bytes.as<uint8_t>();
     rc = run_score_pass(ctx, nullptr);
     if (rc) return rc;
     const int n = in->n_tasks;

@@ -109,6 +109,7 @@ struct svp_ctx
     size_t ev_used = 0;
     size_t arena_budget = (size_t)96 << 30;
     int full_window = 0;   // debug: trace the whole window instead of the provable sub-window
+    const uint8_t *win_bytes = nullptr;   // windows as bytes 0..4 (+ wins.byte_off): align batches -> wins.bytes, polish -> cons0
 
     // ---- align pipeline state (also reused by the polish pipeline) ----
     DevSeqs reads, wins;
@@ -176,6 +177,13 @@ __global__ void pack_kernel(const uint8_t *__restrict__ bytes, const int64_t *__
         if (i < 16) lo |= c << (2 * i); else hi |= c << (2 * (i - 16));
     }
     w2[u * 2] = lo; w2[u * 2 + 1] = hi; wn[u] = nm;
+}
+
+// bases beyond N are N (seqan::Dna5 has 5 values); the score kernel indexes its profile with these bytes
+__global__ void clamp_bases_kernel(uint8_t *__restrict__ b, int64_t n)
+{
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && b[i] > 4) b[i] = 4;
 }
 
 // polish rounds: refresh window lengths / byte offsets from the per-variant state

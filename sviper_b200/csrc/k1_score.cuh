@@ -50,7 +50,10 @@ __global__ void __launch_bounds__(128) k1_score_kernel(const int32_t *__restrict
                                                        const int32_t *__restrict__ task_win,
                                                        const int32_t *__restrict__ task_idx, int ntasks,
                                                        const uint8_t *__restrict__ win_done,
-                                                       SeqStore reads, SeqStore wins, ScoreOut *__restrict__ out,
+                                                       SeqStore reads, SeqStore wins,
+                                                       const uint8_t *__restrict__ win_bytes,
+                                                       const int64_t *__restrict__ win_byte_off,
+                                                       ScoreOut *__restrict__ out,
                                                        uint32_t one /* always 1; opaque to the compiler */)
 {
     using Sh = K1Shape<RPL>;
@@ -60,7 +63,8 @@ __global__ void __launch_bounds__(128) k1_score_kernel(const int32_t *__restrict
     const int slot = blockIdx.x * K1_TASKS_PER_BLOCK + grp;
     uint32_t *prof = k1_smem + grp * Sh::TASK_WORDS;   // prof[c][g][k]
 
-    int R = 0, L = 0, runit = 0, wunit = 0, task = -1;
+    int R = 0, L = 0, runit = 0, task = -1;
+    const uint8_t *wb = win_bytes;   // the window as bytes 0..4 (zero padded behind its end)
     if (slot < ntasks)
     {
         task = task_idx ? task_idx[slot] : slot;
@@ -69,7 +73,7 @@ __global__ void __launch_bounds__(128) k1_score_kernel(const int32_t *__restrict
         else
         {
             R = reads.len[rid]; runit = reads.off32[rid];
-            L = wins.len[wid]; wunit = wins.off32[wid];
+            L = wins.len[wid]; wb = win_bytes + win_byte_off[wid];
         }
     }
     const bool live = task >= 0;
@@ -113,9 +117,13 @@ __global__ void __launch_bounds__(128) k1_score_kernel(const int32_t *__restrict
     uint32_t out_so0 = so[RPL - 1], out_v0 = NEG2, out_so1 = so[RPL - 1], out_v1 = NEG2;
     uint32_t best = so[RPL - 1];
     int colF = 0, colR = 0;
-    uint32_t ww = 0, wn = 0;
-    const uint32_t *w2p = wins.w2 + (size_t)wunit * 2;
-    const uint32_t *wnp = wins.wn + (size_t)wunit;
+    // window characters of the lane's next column pair, fetched one step ahead (a lane's active steps are consecutive)
+    uint32_t ca = 0, cb = 0;
+    if (task >= 0) { ca = __ldg(wb); cb = __ldg(wb + 1); }
+    // lane 0 of a task takes the free first row (S = 0, V = -inf) instead of a neighbour's bottom row; the blend
+    // r * keep + row0 is an IMAD (FMA pipe) where a select would sit on the ALU pipe
+    const uint32_t keep = min((uint32_t)g, one);   // 0 for lane 0, else 1 (through the opaque `one`, so that it stays a multiply)
+    const uint32_t row0_so = (g == 0) ? ROW0_SO : 0u, row0_v = (g == 0) ? NEG2 : 0u;
 
     const int nsteps = __reduce_max_sync(0xffffffffu, live ? (L + 1) / 2 + G - 1 : 0);
     for (int t = 0; t < nsteps; ++t)
@@ -127,16 +135,9 @@ __global__ void __launch_bounds__(128) k1_score_kernel(const int32_t *__restrict
         const int jj = 2 * (t - g);   // window columns jj (a) and jj + 1 (b)
         if (jj >= 0 && jj < L)
         {
-            if (g == 0) { r_so0 = ROW0_SO; r_v0 = NEG2; r_so1 = ROW0_SO; r_v1 = NEG2; }
-            if ((jj & 15) == 0)
-            {
-                ww = __ldg(w2p + (jj >> 4));
-                if ((jj & 31) == 0) wn = __ldg(wnp + (jj >> 5));
-            }
-            // consume two bases: the packer stores 0 in the 2-bit plane under an N, so c = c2 + 4*n is 0..4
-            const int ca = (int)(ww & 3u) + (int)((wn & 1u) << 2);
-            const int cb = (int)((ww >> 2) & 3u) + (int)((wn & 2u) << 1);
-            ww >>= 4; wn >>= 2;
+            r_so0 = r_so0 * keep + row0_so; r_v0 = r_v0 * keep + row0_v;
+            r_so1 = r_so1 * keep + row0_so; r_v1 = r_v1 * keep + row0_v;
+            const uint32_t na = __ldg(wb + jj + 2), nb = __ldg(wb + jj + 3);   // next pair (zero padding behind the end)
             uint32_t pa[NQ * 4], pb[NQ * 4];
             {
                 const uint4 *qa = reinterpret_cast<const uint4 *>(prof + ca * PST + g * KPAD);
@@ -171,22 +172,20 @@ __global__ void __launch_bounds__(128) k1_score_kernel(const int32_t *__restrict
                 h[k] = hB; so[k] = uB;
             }
             out_so0 = uA; out_v0 = vA; out_so1 = uB; out_v1 = vB;
+            ca = na; cb = nb;
             if (g == G - 1)
             {
                 // strict improvement only: the leftmost maximum wins (dp_scout.h:173). Improvements are rare
                 // (a handful per task), so the per-half bookkeeping sits behind a branch.
-                uint32_t m = __vmaxs2(best, uA);
-                if (m != best)
+                if (__vmaxs2(best, __vmaxs2(uA, uB)) != best)
                 {
+                    uint32_t m = __vmaxs2(best, uA);
                     if ((uA & 0xffffu) > (best & 0xffffu)) colF = jj + 1;   // halves are biased positive
                     if ((uA >> 16) > (best >> 16)) colR = jj + 1;
                     best = m;
-                }
-                if (jj + 1 < L)
-                {
-                    m = __vmaxs2(best, uB);
-                    if (m != best)
+                    if (jj + 1 < L)
                     {
+                        m = __vmaxs2(best, uB);
                         if ((uB & 0xffffu) > (best & 0xffffu)) colF = jj + 2;
                         if ((uB >> 16) > (best >> 16)) colR = jj + 2;
                         best = m;
