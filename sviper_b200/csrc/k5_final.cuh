@@ -73,7 +73,11 @@ __global__ void __launch_bounds__(K5_THREADS) k5_final_kernel(const FinalJob *__
         for (int i = T; i <= tb.size; i += K5_THREADS) k5_sg[i] = tb.gapstep[i];
         __syncthreads();
     }
-    auto G = [&](int len) -> double { return SMEM_TABLE ? k5_sg[len] : __ldg(tb.gapstep + len); };
+    // gap lengths are carried as byte offsets into the table (len * 8): a lookup is one load, no index arithmetic
+    auto G = [&](int off) -> double {
+        return SMEM_TABLE ? *reinterpret_cast<const double *>(reinterpret_cast<const char *>(k5_sg) + off)
+                          : __ldg(reinterpret_cast<const double *>(reinterpret_cast<const char *>(tb.gapstep) + off));
+    };
     uint16_t *tr = trace + job.trace_off;
     double *bS = bndS + job.bnd_off, *bV = bndV + job.bnd_off;
     int32_t *bVL = bndVL + job.bnd_off;
@@ -84,14 +88,14 @@ __global__ void __launch_bounds__(K5_THREADS) k5_final_kernel(const FinalJob *__
     {
         const int row0 = band * K5_BAND + T * K5_RPL;   // rows row0+1 .. row0+K5_RPL
         double S[K5_RPL], SO[K5_RPL], H[K5_RPL], HG[K5_RPL];
-        int HL[K5_RPL], sv[K5_RPL];
+        int HL[K5_RPL], sv[K5_RPL];   // HL: horizontal gap length * 8
 #pragma unroll
         for (int k = 0; k < K5_RPL; ++k)
         {
             int row = row0 + k + 1;
             S[k] = (row <= m) ? tb.edge[row] : 0.0;
             SO[k] = __dadd_rn(S[k], GO);
-            H[k] = INF; HL[k] = 1; HG[k] = g1;
+            H[k] = INF; HL[k] = 8; HG[k] = g1;
             sv[k] = (row <= m) ? job.seq[row - 1] : 255;
         }
         double prev_up = (row0 <= m) ? tb.edge[row0] : 0.0;   // S[row0][0]
@@ -105,10 +109,10 @@ __global__ void __launch_bounds__(K5_THREADS) k5_final_kernel(const FinalJob *__
             const int par = t & 1;
             if (col >= 1 && col <= n && live)
             {
-                double up_s, up_v, up_vg; int up_vl;
+                double up_s, up_v, up_vg; int up_vl;   // up_vl: vertical gap length * 8
                 if (T == 0)
                 {
-                    if (band == 0) { up_s = tb.edge[col]; up_v = INF; up_vl = 1; up_vg = g1; }
+                    if (band == 0) { up_s = tb.edge[col]; up_v = INF; up_vl = 8; up_vg = g1; }
                     else { up_s = bS[col]; up_v = bV[col]; up_vl = bVL[col]; up_vg = G(up_vl); }
                 }
                 else
@@ -117,43 +121,54 @@ __global__ void __launch_bounds__(K5_THREADS) k5_final_kernel(const FinalJob *__
                     up_vg = shVG[par ^ 1][T - 1];
                 }
                 const int hc = job.ref[col - 1];
-                const bool endcol = (col == n);
                 double diag = prev_up;
                 prev_up = up_s;
                 double up_so = __dadd_rn(up_s, GO);
+                double Vk[K5_RPL];
                 uint32_t tw = 0;
 #pragma unroll
                 for (int k = 0; k < K5_RPL; ++k)
                 {
-                    double inter = __dadd_rn(diag, (hc == sv[k]) ? MM : MX);
+                    const double inter = __dadd_rn(diag, (hc == sv[k]) ? MM : MX);
                     diag = S[k];
-                    double hext = __dadd_rn(H[k], HG[k]);
-                    double hopn = SO[k];
-                    uint32_t code;
-                    double hh;
                     // the step value of a gap that gets extended is looked up before the compare resolves
-                    const double hg_ext = G(HL[k] + 1), vg_ext = G(up_vl + 1);
-                    if (hext < hopn) { hh = hopn; HL[k] = 1; HG[k] = g1; code = 0u; }
-                    else { hh = hext; HL[k] += 1; HG[k] = hg_ext; code = 1u; }
+                    const double hg_ext = G(HL[k] + 8), vg_ext = G(up_vl + 8);
+                    const double hext = __dadd_rn(H[k], HG[k]);
+                    const bool hx = !(hext < SO[k]);              // tie -> extension (dp_formula.h:152-163)
+                    const double hh = hx ? hext : SO[k];
+                    HL[k] = hx ? HL[k] + 8 : 8;
+                    HG[k] = hx ? hg_ext : g1;
                     H[k] = hh;
-                    double vext = __dadd_rn(up_v, up_vg);
-                    if (vext < up_so) { up_v = up_so; up_vl = 1; up_vg = g1; }
-                    else { up_v = vext; up_vl += 1; up_vg = vg_ext; code |= 2u; }
-                    double gap; uint32_t gsel;
-                    if (up_v < hh) { gap = hh; gsel = 8u; } else { gap = up_v; gsel = 4u; }
-                    double sn;
-                    if (inter < gap) { sn = gap; code |= gsel; } else sn = inter;
-                    if (endcol && k == endk)
-                    {
-                        FinalEnd e; e.S = sn; e.H = hh; e.V = up_v;
-                        ends[blockIdx.x] = e;
-                        if (up_v == sn) code = (code & 3u) | 4u;        // dp_algorithm_impl.h:1212-1229
-                        else if (hh == sn) code = (code & 3u) | 8u;
-                    }
+                    const double vext = __dadd_rn(up_v, up_vg);
+                    const bool vx = !(vext < up_so);
+                    up_v = vx ? vext : up_so;
+                    up_vl = vx ? up_vl + 8 : 8;
+                    up_vg = vx ? vg_ext : g1;
+                    const bool gv = !(up_v < hh);                 // tie -> vertical
+                    const double gap = gv ? up_v : hh;
+                    const bool dg = !(inter < gap);               // tie -> diagonal
+                    const double sn = dg ? inter : gap;
+                    const uint32_t code = (hx ? 1u : 0u) | (vx ? 2u : 0u) | (dg ? 0u : (gv ? 4u : 8u));
                     tw |= code << (4 * k);
+                    Vk[k] = up_v;
                     S[k] = sn;
                     up_so = __dadd_rn(sn, GO);
                     SO[k] = up_so;
+                }
+                if (col == n && (unsigned)endk < (unsigned)K5_RPL)
+                {
+                    // the end cell (m, n): report S/H/V and apply the end-cell correction (dp_algorithm_impl.h:1212-1229)
+#pragma unroll
+                    for (int k = 0; k < K5_RPL; ++k)
+                        if (k == endk)
+                        {
+                            FinalEnd e; e.S = S[k]; e.H = H[k]; e.V = Vk[k];
+                            ends[blockIdx.x] = e;
+                            uint32_t c = (tw >> (4 * k)) & 15u;
+                            if (Vk[k] == S[k]) c = (c & 3u) | 4u;
+                            else if (H[k] == S[k]) c = (c & 3u) | 8u;
+                            tw = (tw & ~(15u << (4 * k))) | (c << (4 * k));
+                        }
                 }
                 shS[par][T] = S[K5_RPL - 1]; shV[par][T] = up_v; shVL[par][T] = up_vl; shVG[par][T] = up_vg;
                 if (T == K5_THREADS - 1 && band + 1 < nbands) { bS[col] = S[K5_RPL - 1]; bV[col] = up_v; bVL[col] = up_vl; }
