@@ -35,7 +35,7 @@ struct FinalJob
     const uint8_t *ref;   // H, length n (device)
     const uint8_t *seq;   // V, length m (device)
     int32_t n, m;
-    int64_t trace_off;    // u16 units: (n + K5_THREADS) * row_threads
+    int64_t trace_off;    // u32 units: ((n + 1) / 2 + K5_THREADS) * row_threads
     int32_t row_threads;  // nbands * K5_THREADS
     int64_t bnd_off;      // per-column band boundary (n + 1 entries)
     int32_t valid;
@@ -58,15 +58,16 @@ struct K5Tables
 template <bool SMEM_TABLE>
 __global__ void __launch_bounds__(K5_THREADS) k5_final_kernel(const FinalJob *__restrict__ jobs, K5Tables tb,
                                                              double MM, double MX, double GO, double INF,
-                                                             uint16_t *__restrict__ trace, double *__restrict__ bndS,
+                                                             uint32_t *__restrict__ trace, double *__restrict__ bndS,
                                                              double *__restrict__ bndV, int32_t *__restrict__ bndVL,
                                                              FinalEnd *__restrict__ ends)
 {
     const FinalJob job = jobs[blockIdx.x];
     if (!job.valid) return;
     const int T = threadIdx.x, n = job.n, m = job.m;
-    __shared__ double shS[2][K5_THREADS], shV[2][K5_THREADS], shVG[2][K5_THREADS];
-    __shared__ int shVL[2][K5_THREADS];
+    // bottom-row handoff to the thread below, double buffered by step parity, two columns (A, B) per step
+    __shared__ double shS[2][2][K5_THREADS], shV[2][2][K5_THREADS];
+    __shared__ int shVL[2][2][K5_THREADS];
     extern __shared__ double k5_sg[];
     if (SMEM_TABLE)
     {
@@ -78,7 +79,7 @@ __global__ void __launch_bounds__(K5_THREADS) k5_final_kernel(const FinalJob *__
         return SMEM_TABLE ? *reinterpret_cast<const double *>(reinterpret_cast<const char *>(k5_sg) + off)
                           : __ldg(reinterpret_cast<const double *>(reinterpret_cast<const char *>(tb.gapstep) + off));
     };
-    uint16_t *tr = trace + job.trace_off;
+    uint32_t *tr = trace + job.trace_off;
     double *bS = bndS + job.bnd_off, *bV = bndV + job.bnd_off;
     int32_t *bVL = bndVL + job.bnd_off;
     const int nbands = job.row_threads / K5_THREADS;
@@ -101,78 +102,118 @@ __global__ void __launch_bounds__(K5_THREADS) k5_final_kernel(const FinalJob *__
         double prev_up = (row0 <= m) ? tb.edge[row0] : 0.0;   // S[row0][0]
         const bool live = row0 < m;                            // this thread owns at least one real row
         const int endk = m - 1 - row0;                         // slot of the last row, if this thread owns it
-        const int nsteps = n + K5_THREADS - 1;
+        // every step advances TWO columns (A = 2(t-T)+1, B = A+1): the fp64 dependency chains of the two columns
+        // are independent (cell (k, B) only needs cell (k, A)), which doubles the instruction-level parallelism
+        // and halves the number of block-wide barriers. An odd n gets one harmless extra column.
+        const int nsteps = (n + 1) / 2 + K5_THREADS - 1;
         const size_t tcol = (size_t)band * K5_THREADS + T;
         for (int t = 0; t < nsteps; ++t)
         {
-            const int col = t - T + 1;
+            const int colA = 2 * (t - T) + 1, colB = colA + 1;
             const int par = t & 1;
-            if (col >= 1 && col <= n && live)
+            if (colA >= 1 && colA <= n && live)
             {
-                double up_s, up_v, up_vg; int up_vl;   // up_vl: vertical gap length * 8
+                double uSa, uVa, uGa, uSb, uVb, uGb; int uLa, uLb;   // uL*: vertical gap length * 8
                 if (T == 0)
                 {
-                    if (band == 0) { up_s = tb.edge[col]; up_v = INF; up_vl = 8; up_vg = g1; }
-                    else { up_s = bS[col]; up_v = bV[col]; up_vl = bVL[col]; up_vg = G(up_vl); }
+                    if (band == 0)
+                    {
+                        uSa = tb.edge[colA]; uSb = tb.edge[colB]; uVa = INF; uVb = INF; uLa = 8; uLb = 8; uGa = g1; uGb = g1;
+                    }
+                    else
+                    {
+                        uSa = bS[colA]; uVa = bV[colA]; uLa = bVL[colA]; uGa = G(uLa);
+                        uSb = bS[colB]; uVb = bV[colB]; uLb = bVL[colB]; uGb = G(uLb);
+                    }
                 }
                 else
                 {
-                    up_s = shS[par ^ 1][T - 1]; up_v = shV[par ^ 1][T - 1]; up_vl = shVL[par ^ 1][T - 1];
-                    up_vg = shVG[par ^ 1][T - 1];
+                    uSa = shS[par ^ 1][0][T - 1]; uVa = shV[par ^ 1][0][T - 1]; uLa = shVL[par ^ 1][0][T - 1]; uGa = G(uLa);
+                    uSb = shS[par ^ 1][1][T - 1]; uVb = shV[par ^ 1][1][T - 1]; uLb = shVL[par ^ 1][1][T - 1]; uGb = G(uLb);
                 }
-                const int hc = job.ref[col - 1];
-                double diag = prev_up;
-                prev_up = up_s;
-                double up_so = __dadd_rn(up_s, GO);
-                double Vk[K5_RPL];
-                uint32_t tw = 0;
+                const int hcA = job.ref[colA - 1], hcB = job.ref[colB - 1];   // ref is padded behind its end
+                double dA = prev_up;      // S(row above, A - 1)
+                prev_up = uSb;            // S(row above, B): the diagonal of the next step's column A
+                double dB = uSa;          // S(row above, A)
+                double uOa = __dadd_rn(uSa, GO), uOb = __dadd_rn(uSb, GO);
+                double VkA[K5_RPL], VkB[K5_RPL], HkA[K5_RPL], SkA[K5_RPL];
+                uint32_t twA = 0, twB = 0;
 #pragma unroll
                 for (int k = 0; k < K5_RPL; ++k)
                 {
-                    const double inter = __dadd_rn(diag, (hc == sv[k]) ? MM : MX);
-                    diag = S[k];
-                    // the step value of a gap that gets extended is looked up before the compare resolves
-                    const double hg_ext = G(HL[k] + 8), vg_ext = G(up_vl + 8);
-                    const double hext = __dadd_rn(H[k], HG[k]);
-                    const bool hx = !(hext < SO[k]);              // tie -> extension (dp_formula.h:152-163)
-                    const double hh = hx ? hext : SO[k];
-                    HL[k] = hx ? HL[k] + 8 : 8;
-                    HG[k] = hx ? hg_ext : g1;
-                    H[k] = hh;
-                    const double vext = __dadd_rn(up_v, up_vg);
-                    const bool vx = !(vext < up_so);
-                    up_v = vx ? vext : up_so;
-                    up_vl = vx ? up_vl + 8 : 8;
-                    up_vg = vx ? vg_ext : g1;
-                    const bool gv = !(up_v < hh);                 // tie -> vertical
-                    const double gap = gv ? up_v : hh;
-                    const bool dg = !(inter < gap);               // tie -> diagonal
-                    const double sn = dg ? inter : gap;
-                    const uint32_t code = (hx ? 1u : 0u) | (vx ? 2u : 0u) | (dg ? 0u : (gv ? 4u : 8u));
-                    tw |= code << (4 * k);
-                    Vk[k] = up_v;
-                    S[k] = sn;
-                    up_so = __dadd_rn(sn, GO);
-                    SO[k] = up_so;
+                    // ---- column A: left neighbour = the state arrays (column A - 1)
+                    const double interA = __dadd_rn(dA, (hcA == sv[k]) ? MM : MX);
+                    dA = S[k];
+                    const double hgA = G(HL[k] + 8), vgA = G(uLa + 8);     // looked up before the compares resolve
+                    const double hextA = __dadd_rn(H[k], HG[k]);
+                    const bool hxA = !(hextA < SO[k]);             // tie -> extension (dp_formula.h:152-163)
+                    const double hhA = hxA ? hextA : SO[k];
+                    const int hlA = hxA ? HL[k] + 8 : 8;
+                    const double hsA = hxA ? hgA : g1;
+                    const double vextA = __dadd_rn(uVa, uGa);
+                    const bool vxA = !(vextA < uOa);
+                    uVa = vxA ? vextA : uOa;
+                    uLa = vxA ? uLa + 8 : 8;
+                    uGa = vxA ? vgA : g1;
+                    const bool gvA = !(uVa < hhA);                 // tie -> vertical
+                    const double gapA = gvA ? uVa : hhA;
+                    const bool dgA = !(interA < gapA);             // tie -> diagonal
+                    const double snA = dgA ? interA : gapA;
+                    twA |= ((hxA ? 1u : 0u) | (vxA ? 2u : 0u) | (dgA ? 0u : (gvA ? 4u : 8u))) << (4 * k);
+                    uOa = __dadd_rn(snA, GO);
+                    VkA[k] = uVa; HkA[k] = hhA; SkA[k] = snA;
+                    // ---- column B: left neighbour = column A of this row
+                    const double interB = __dadd_rn(dB, (hcB == sv[k]) ? MM : MX);
+                    dB = snA;
+                    const double hgB = G(hlA + 8), vgB = G(uLb + 8);
+                    const double hextB = __dadd_rn(hhA, hsA);
+                    const bool hxB = !(hextB < uOa);
+                    const double hhB = hxB ? hextB : uOa;
+                    HL[k] = hxB ? hlA + 8 : 8;
+                    HG[k] = hxB ? hgB : g1;
+                    H[k] = hhB;
+                    const double vextB = __dadd_rn(uVb, uGb);
+                    const bool vxB = !(vextB < uOb);
+                    uVb = vxB ? vextB : uOb;
+                    uLb = vxB ? uLb + 8 : 8;
+                    uGb = vxB ? vgB : g1;
+                    const bool gvB = !(uVb < hhB);
+                    const double gapB = gvB ? uVb : hhB;
+                    const bool dgB = !(interB < gapB);
+                    const double snB = dgB ? interB : gapB;
+                    twB |= ((hxB ? 1u : 0u) | (vxB ? 2u : 0u) | (dgB ? 0u : (gvB ? 4u : 8u))) << (4 * k);
+                    VkB[k] = uVb;
+                    S[k] = snB;
+                    uOb = __dadd_rn(snB, GO);
+                    SO[k] = uOb;
                 }
-                if (col == n && (unsigned)endk < (unsigned)K5_RPL)
+                if ((colA == n || colB == n) && (unsigned)endk < (unsigned)K5_RPL)
                 {
                     // the end cell (m, n): report S/H/V and apply the end-cell correction (dp_algorithm_impl.h:1212-1229)
+                    const bool inA = (colA == n);
 #pragma unroll
                     for (int k = 0; k < K5_RPL; ++k)
                         if (k == endk)
                         {
-                            FinalEnd e; e.S = S[k]; e.H = H[k]; e.V = Vk[k];
+                            FinalEnd e;
+                            e.S = inA ? SkA[k] : S[k]; e.H = inA ? HkA[k] : H[k]; e.V = inA ? VkA[k] : VkB[k];
                             ends[blockIdx.x] = e;
+                            uint32_t tw = inA ? twA : twB;
                             uint32_t c = (tw >> (4 * k)) & 15u;
-                            if (Vk[k] == S[k]) c = (c & 3u) | 4u;
-                            else if (H[k] == S[k]) c = (c & 3u) | 8u;
+                            if (e.V == e.S) c = (c & 3u) | 4u;
+                            else if (e.H == e.S) c = (c & 3u) | 8u;
                             tw = (tw & ~(15u << (4 * k))) | (c << (4 * k));
+                            if (inA) twA = tw; else twB = tw;
                         }
                 }
-                shS[par][T] = S[K5_RPL - 1]; shV[par][T] = up_v; shVL[par][T] = up_vl; shVG[par][T] = up_vg;
-                if (T == K5_THREADS - 1 && band + 1 < nbands) { bS[col] = S[K5_RPL - 1]; bV[col] = up_v; bVL[col] = up_vl; }
-                tr[(size_t)t * job.row_threads + tcol] = (uint16_t)tw;
+                shS[par][0][T] = SkA[K5_RPL - 1]; shV[par][0][T] = uVa; shVL[par][0][T] = uLa;
+                shS[par][1][T] = S[K5_RPL - 1]; shV[par][1][T] = uVb; shVL[par][1][T] = uLb;
+                if (T == K5_THREADS - 1 && band + 1 < nbands)
+                {
+                    bS[colA] = SkA[K5_RPL - 1]; bV[colA] = uVa; bVL[colA] = uLa;
+                    bS[colB] = S[K5_RPL - 1]; bV[colB] = uVb; bVL[colB] = uLb;
+                }
+                tr[(size_t)t * job.row_threads + tcol] = twA | (twB << 16);
             }
             __syncthreads();
         }
@@ -195,7 +236,7 @@ struct CigarOut
 // about one per 32. All lanes carry the same (col, row, CIGAR) state; lane 0 writes.
 constexpr int K5TB_WARPS = 4;
 __global__ void __launch_bounds__(K5TB_WARPS * 32) k5_traceback_kernel(
-    const FinalJob *__restrict__ jobs, int njobs, const uint16_t *__restrict__ trace, const FinalEnd *__restrict__ ends,
+    const FinalJob *__restrict__ jobs, int njobs, const uint32_t *__restrict__ trace, const FinalEnd *__restrict__ ends,
     double INF, char *__restrict__ cig_op, uint32_t *__restrict__ cig_cnt, int cap, CigarOut *__restrict__ out)
 {
     const int j = blockIdx.x * K5TB_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
@@ -204,7 +245,7 @@ __global__ void __launch_bounds__(K5TB_WARPS * 32) k5_traceback_kernel(
     if (!job.valid) return;
     char *op = cig_op + (size_t)j * cap;
     uint32_t *cnt = cig_cnt + (size_t)j * cap;
-    const uint16_t *tr = trace + job.trace_off;
+    const uint32_t *tr = trace + job.trace_off;
     int ne = 0;          // elements emitted (reverse order)
     char last = 0; uint32_t run = 0;
     auto emit = [&](char c, uint32_t k) {
@@ -226,8 +267,8 @@ __global__ void __launch_bounds__(K5TB_WARPS * 32) k5_traceback_kernel(
         o.score = ends[j].S;
     auto codeat = [&](int c, int r) -> uint32_t {
         const int slot = r - 1, tg = slot / K5_RPL;
-        const int t = c - 1 + (tg % K5_THREADS);
-        uint32_t w = tr[(size_t)t * job.row_threads + tg];
+        const int t = ((c - 1) >> 1) + (tg % K5_THREADS);
+        uint32_t w = tr[(size_t)t * job.row_threads + tg] >> (16 * ((c - 1) & 1));
         return (w >> (4 * (slot % K5_RPL))) & 15u;
     };
     const unsigned FULL = 0xffffffffu;
