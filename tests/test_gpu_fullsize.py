@@ -1,0 +1,113 @@
+"""GPU tests at BASELINE.json's full shapes. The oracle is too slow to re-run whole batches at these sizes, so
+besides a few direct oracle comparisons the CUDA path is checked through size-independent properties:
+batch-composition independence, idempotence of polishing, CIGAR/sequence length accounting, determinism."""
+import numpy as np
+import pytest
+
+from tests import refcases as rc
+
+pytestmark = pytest.mark.gpu
+orc, synth = rc.orc, rc.synth
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    from sviper_b200 import api
+    c = api.Context(0)
+    yield c
+    c.close()
+
+
+def same(a, b):
+    return (np.array_equal(a["polished"], b["polished"]) and np.array_equal(a["cov"], b["cov"]) and
+            (a["rounds"], a["subst"], a["ins"], a["dele"]) == (b["rounds"], b["subst"], b["ins"], b["dele"]) and
+            a["mappQ_mean"] == b["mappQ_mean"] and a.get("cigar") == b.get("cigar") and
+            a["final_score"] == b["final_score"])
+
+
+@pytest.fixture(scope="module")
+def config1_batch():
+    """configs[1] shape: DELs 50..1000 bp, 30x 2x150 reads, -k 400, 5% noisy consensus (bench.py's workload)"""
+    import bench
+    return bench.make_batch(24, seed=77)
+
+
+def test_config1_oracle_on_full_size_variants(ctx, config1_batch):
+    vs = config1_batch[:3]
+    got = ctx.polish_batch(vs, with_final=True)
+    for v, g in zip(vs, got):
+        r1p, r2p = rc.packed(v)
+        cfg = rc.oracle_cfg(v, r1p, r2p)
+        seq, cov = orc.polish_to_perfection(cfg, *r1p, *r2p, v["consensus"])
+        assert np.array_equal(seq, g["polished"]) and np.array_equal(cov, g["cov"])
+        assert (cfg.rounds, cfg.subst, cfg.ins, cfg.del_) == (g["rounds"], g["subst"], g["ins"], g["dele"])
+        sc, ops = orc.align_convex(v["ref_part"], seq)
+        assert sc == g["final_score"] and orc.cigar(ops) == g["cigar"]
+
+
+def test_config1_properties(ctx, config1_batch):
+    vs = config1_batch
+    got = ctx.polish_batch(vs, with_final=True)
+    # determinism: the same batch again (different arena contents, same results)
+    again = ctx.polish_batch(vs, with_final=True)
+    assert all(same(a, b) for a, b in zip(got, again))
+    # batch-composition independence: a variant alone, and in a shuffled sub-batch, gives identical bits
+    for i in (0, 7, 23):
+        assert same(ctx.polish_batch([vs[i]], with_final=True)[0], got[i])
+    order = [5, 3, 11, 2]
+    sub = ctx.polish_batch([vs[i] for i in order], with_final=True)
+    assert all(same(s, got[i]) for s, i in zip(sub, order))
+    n_truth = 0
+    for v, g in zip(vs, got):
+        # CIGAR accounting (getCigarString, bam_io/cigar.h:354-420): M+D spans the reference part, M+I the polished seq
+        ref_span = sum(n for o, n in g["cigar"] if o in "MD")
+        seq_span = sum(n for o, n in g["cigar"] if o in "MI")
+        assert ref_span == len(v["ref_part"]) and seq_span == len(g["polished"])
+        assert g["n_cigar"] == len(g["cigar"]) and all(n > 0 for _, n in g["cigar"])
+        assert all(a[0] != b[0] for a, b in zip(g["cigar"], g["cigar"][1:]))            # run-length encoded
+        # the flanks are copied verbatim (polishing.h:247,287)
+        f = v["flank"]
+        assert np.array_equal(g["polished"][:f], v["consensus"][:f]) and np.array_equal(g["polished"][-f:], v["consensus"][-f:])
+        assert 2 <= g["rounds"] <= 30 and len(g["cov"]) >= len(g["polished"]) - 1
+        n_truth += int(np.array_equal(g["polished"], v["truth"]))
+    assert n_truth >= 0.7 * len(vs), "polishing should recover most of the synthetic truths (%d/%d)" % (n_truth, len(vs))
+    # idempotence: polishing an already polished window changes nothing (one round per phase, polishing.h:327-343)
+    vs2 = [dict(v, consensus=g["polished"]) for v, g in zip(vs, got)]
+    got2 = ctx.polish_batch(vs2, with_final=True)
+    for g, g2 in zip(got, got2):
+        if g["rounds"] < 30:
+            assert np.array_equal(g2["polished"], g["polished"])
+            assert (g2["rounds"], g2["subst"], g2["ins"], g2["dele"]) == (2, 0, 0, 0)
+            assert g2["cigar"] == g["cigar"] and g2["final_score"] == g["final_score"]
+
+
+def test_config4_large_insertion_window(ctx):
+    """configs[3] shape: kb-scale insertion with -k 1000 (window ~5 kb, final DP ~5k x 3k, multi-band rows)"""
+    v = synth.make_variant(41, "INS", svlen=2000, k=1000, cov=5, cons_err=0.02)
+    g = ctx.polish_batch([v], with_final=True)[0]
+    r1p, r2p = rc.packed(v)
+    cfg = rc.oracle_cfg(v, r1p, r2p)
+    seq, cov = orc.polish_to_perfection(cfg, *r1p, *r2p, v["consensus"])
+    assert np.array_equal(seq, g["polished"]) and np.array_equal(cov, g["cov"])
+    assert (cfg.rounds, cfg.subst, cfg.ins, cfg.del_) == (g["rounds"], g["subst"], g["ins"], g["dele"])
+    sc, ops = orc.align_convex(v["ref_part"], seq)
+    assert sc == g["final_score"] and orc.cigar(ops) == g["cigar"]
+    assert any(o == "I" and n > 1500 for o, n in g["cigar"])
+
+
+def test_mixed_read_lengths_and_ns_in_one_batch(ctx):
+    """ragged batch: 150 bp and 250 bp libraries, N bases, a dummy mate, windows of different size"""
+    vs = [synth.make_variant(51, "DEL", svlen=80, k=200, cov=8, cons_err=0.03, n_rate=0.004),
+          synth.make_variant(52, "INS", svlen=60, k=150, cov=8, read_len=250, cons_err=0.03, frag_mean=560.0),
+          synth.make_variant(53, "DEL", svlen=400, k=300, cov=6, cons_err=0.05)]
+    vs[0]["reads2"][-1] = np.zeros(0, np.uint8); vs[0]["quals2"][-1] = np.zeros(0, np.uint8)
+    vs[1]["ins_mean"], vs[1]["ins_sd"] = 300.0, 150.0
+    got = ctx.polish_batch(vs, with_final=True)
+    for v, g in zip(vs, got):
+        r1p, r2p = rc.packed(v)
+        cfg = rc.oracle_cfg(v, r1p, r2p)
+        seq, cov = orc.polish_to_perfection(cfg, *r1p, *r2p, v["consensus"])
+        assert np.array_equal(seq, g["polished"]) and np.array_equal(cov, g["cov"])
+        assert (cfg.rounds, cfg.subst, cfg.ins, cfg.del_) == (g["rounds"], g["subst"], g["ins"], g["dele"])
+        sc, ops = orc.align_convex(v["ref_part"], seq)
+        assert sc == g["final_score"] and orc.cigar(ops) == g["cigar"]
