@@ -25,7 +25,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 READ_LEN, K_FLANK, COV = 150, 400, 30
-K1_DRAM_BYTES_PER_LAUNCH = 1.6e6   # from the committed ncu capture (see profiles/)
+K1_DRAM_BYTES_PER_LAUNCH = 1.7e6   # dram__bytes_read.sum + dram__bytes_write.sum, profiles/r1_k1_score_ncu_raw.csv
 
 
 def make_batch(n_variants, seed):
