@@ -44,6 +44,12 @@ svp_ctx *svp_create(int cuda_device, void *cuda_stream)
     }
     cudaEventCreate(&ctx->ev0);
     cudaEventCreate(&ctx->ev1);
+    cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming);
+    for (int c = 0; c < svp::TC_N; ++c)
+    {
+        if (cudaStreamCreateWithFlags(&ctx->side[c], cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return nullptr; }
+        cudaEventCreateWithFlags(&ctx->ev_side[c], cudaEventDisableTiming);
+    }
     if (cudaHostAlloc((void **)&ctx->h_active, 64, cudaHostAllocDefault) != cudaSuccess) { delete ctx; return nullptr; }
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) ctx->arena_budget = (size_t)(free_b * 0.6);
@@ -76,6 +82,8 @@ void svp_destroy(svp_ctx *ctx)
     for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
     cudaEventDestroy(ctx->ev0);
     cudaEventDestroy(ctx->ev1);
+    cudaEventDestroy(ctx->ev_fork);
+    for (int c = 0; c < svp::TC_N; ++c) { cudaEventDestroy(ctx->ev_side[c]); cudaStreamDestroy(ctx->side[c]); }
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }

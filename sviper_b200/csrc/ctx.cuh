@@ -101,6 +101,8 @@ struct svp_ctx
     bool own_stream = false;
     std::string err;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaStream_t side[svp::TC_N] = {nullptr};        // traced-pass class kernels run side by side
+    cudaEvent_t ev_fork = nullptr, ev_side[svp::TC_N] = {nullptr};
     int n_launches = 0;
     double ms[ST_N] = {0};
     bool timing = false;

@@ -35,8 +35,8 @@ constexpr int KT_NEG = INT32_MIN / 2;   // seqan/align/dp_cell.h:144-145
 // it would itself be on a co-optimal path and therefore inside the band), so every trace decision the
 // traceback reads is identical to the full matrix. full_window != 0 disables both restrictions.
 // ---------------------------------------------------------------------------------------------
-constexpr int KB_MAXW16 = 15;   // 2w+1 <= 32 diagonals: 16 lanes x 2 diagonals
-constexpr int KB_MAXW32 = 31;   // 2w+1 <= 64 diagonals: 32 lanes x 2 diagonals
+constexpr int KB_MAXW16 = 15;   // 2w+1 <= 32 diagonals: 8 lanes x 4 diagonals
+constexpr int KB_MAXW32 = 31;   // 2w+1 <= 64 diagonals: 16 lanes x 4 diagonals
 
 __host__ __device__ inline int kb_row_words(int R) { return (R >> 3) + 1; }   // trace words per diagonal (rows 0..R)
 
@@ -70,7 +70,7 @@ __global__ void plan_kernel(const int32_t *__restrict__ task_read, const int32_t
     {
         p.band_w = slack; p.dlo = p.end_col - R - slack;
         cls = slack <= KB_MAXW16 ? TC_BAND16 : TC_BAND32;
-        tunits[t] = (int64_t)(2 * slack + 2) * kb_row_words(R);
+        tunits[t] = (int64_t)(slack <= KB_MAXW16 ? 32 : 64) * kb_row_words(R);   // every diagonal the lanes own
     }
     else
     {
@@ -187,35 +187,40 @@ __global__ void __launch_bounds__(KT_WARPS * 32) k1_trace_kernel(const TracePlan
 }
 
 // ---------------------------------------------------------------------------------------------
-// K1b: BANDED traced pass. LPA lanes per alignment (128 / LPA alignments per block), lane l owns the two
-// diagonals d = 2l, 2l+1 of the band (d = (j - i) - dlo). Step a covers the anti-diagonal i + j = a: every
-// lane computes the one cell of its diagonal with d == a - dlo (mod 2). Predecessors:
-//   diagonal (i-1, j-1): same diagonal, the lane's own previous value
-//   up       (i-1, j)  : diagonal d+1, computed one step earlier (own register, or lane l+1 via shuffle)
-//   left     (i, j-1)  : diagonal d-1, computed one step earlier (own register, or lane l-1 via shuffle)
-// Row 0 (S = 0, free begin) and DP column 0 (S = go + (i-1) ge) are "computed" as their initial values,
-// anything else outside the matrix or the band is -infinity.
-// Trace: 4 bits per cell as in the strip kernel; a lane collects the nibbles of 8 consecutive rows of one
+// K1b: BANDED traced pass. LPA lanes per alignment (128 / LPA alignments per block), lane l owns the DPL
+// consecutive diagonals d = DPL*l + x (x = 0..DPL-1; d = (j - i) - dlo). One iteration covers two
+// anti-diagonals: the even step computes the cells of the even slots x, the odd step those of the odd slots.
+// Slots 2p and 2p+1 of a lane work on the same read row i = i0 - p in one iteration (i0 advances by one per
+// iteration), so the read base is fetched once per slot pair. Predecessors:
+//   diagonal (i-1, j-1): same diagonal, the slot's own previous value
+//   up       (i-1, j)  : diagonal d+1 = slot x+1 (or lane l+1's slot 0 via shuffle), computed one step earlier
+//   left     (i, j-1)  : diagonal d-1 = slot x-1 (or lane l-1's last slot via shuffle), computed one step earlier
+// Row 0 (S = 0, free begin) and DP column 0 (S = go + (i-1) ge) take their initial values, anything else
+// outside the matrix or the band is -infinity; all of that is select-based (no divergent early exits).
+// Trace: 4 bits per cell as in the strip kernel; a slot collects the nibbles of 8 consecutive rows of its
 // diagonal into a word: trace[d * RW + (i >> 3)], RW = kb_row_words(R).
 // ---------------------------------------------------------------------------------------------
 constexpr int KB_THREADS = 128;
+constexpr int KB_DPL = 4;                                   // diagonals per lane
 constexpr int KB_RMAX = SVP_MAX_READ_LEN + 8;               // staged read bytes
 constexpr int KB_WMAX = SVP_MAX_READ_LEN + 2 * KB_MAXW32 + 8;   // staged window bytes (columns jbase .. e)
 constexpr int KB_SEQ_BYTES = KB_RMAX + KB_WMAX + 8;
 
-template <int LPA>
+template <int LPA, int DPL>
 __global__ void __launch_bounds__(KB_THREADS) k1_band_kernel(const TracePlan *__restrict__ plans, int ntasks,
                                                             const int32_t *__restrict__ task_idx, SeqStore reads,
                                                             SeqStore wins, const int64_t *__restrict__ TE,
                                                             uint32_t *__restrict__ trace)
 {
+    static_assert(DPL % 2 == 0 && LPA <= 32 && 32 % LPA == 0, "band kernel shape");
     constexpr int APB = KB_THREADS / LPA;   // alignments per block
+    constexpr int NP = DPL / 2;             // slot pairs per lane
     __shared__ uint8_t kb_seq[APB][KB_SEQ_BYTES];
     const int l = threadIdx.x % LPA, grp = threadIdx.x / LPA;
     const int slot = blockIdx.x * APB + grp;
-    const unsigned gmask = (LPA == 32) ? 0xffffffffu : (0xffffu << (16 * ((threadIdx.x >> 4) & 1)));
+    const unsigned gmask = (LPA == 32) ? 0xffffffffu : (((1u << (LPA & 31)) - 1u) << (LPA * ((threadIdx.x & 31) / LPA)));
     const bool live = slot < ntasks;
-    int R = 0, e = 0, dlo = 0, B = 0, rc = 0, runit = 0, wunit = 0, jbase = 0;
+    int R = 0, e = 0, dlo = 0, rc = 0, runit = 0, wunit = 0, jbase = 0;
     uint32_t *tr = trace;
     if (live)
     {
@@ -223,7 +228,7 @@ __global__ void __launch_bounds__(KB_THREADS) k1_band_kernel(const TracePlan *__
         const TracePlan pl = plans[task];
         R = reads.len[pl.read_id]; runit = reads.off32[pl.read_id];
         wunit = wins.off32[pl.win_id];
-        e = pl.end_col; dlo = pl.dlo; B = 2 * pl.band_w + 1; rc = pl.is_rc;
+        e = pl.end_col; dlo = pl.dlo; rc = pl.is_rc;
         tr = trace + TE[task];
         jbase = dlo > 0 ? dlo : 0;   // window columns jbase+1 .. e are staged at sW[j - jbase]
     }
@@ -238,24 +243,31 @@ __global__ void __launch_bounds__(KB_THREADS) k1_band_kernel(const TracePlan *__
     for (int j = jbase + 1 + l; j <= e; j += LPA) sW[j - jbase] = (uint8_t)seq_base(wins, wunit, j - 1);
     __syncwarp(gmask);
 
-    // own diagonals: slot 0 = 2l, slot 1 = 2l + 1; values of the last cell computed on each
-    int S0 = KT_NEG, H0 = KT_NEG, V0 = KT_NEG, S1 = KT_NEG, H1 = KT_NEG, V1 = KT_NEG;
-    uint32_t acc0 = 0, acc1 = 0;
+    // values of the last cell computed on each own diagonal. A slot that has no cell inside the matrix in some
+    // step keeps a stale value: a cell inside the matrix only ever reads neighbours that are inside too (or the
+    // lane-edge -infinity), and those are by construction the most recent cells of their slots.
+    int S[DPL], H[DPL], V[DPL];
+    uint32_t acc[DPL];
+#pragma unroll
+    for (int x = 0; x < DPL; ++x) { S[x] = KT_NEG; H[x] = KT_NEG; V[x] = KT_NEG; acc[x] = 0; }
     const int RW = kb_row_words(R);
-    // first step: the smallest anti-diagonal with a cell in the matrix, rounded down to even parity (slot 0)
+    // first step: the smallest anti-diagonal with a cell in the matrix, rounded down to even parity (even slots)
     int a_first = jbase;
     if ((a_first - dlo) & 1) --a_first;
     const int a_last = R + e;
-    const int d0 = 2 * l, d1 = 2 * l + 1;
+    const int my_n = live ? (a_last - a_first + 2) / 2 : 0;                 // iterations of this alignment
+    const int nsteps = __reduce_max_sync(0xffffffffu, my_n);
+    int i0 = (a_first - dlo - DPL * l) >> 1;                                // row of slot pair 0 (exact: even)
+    const int jd = dlo + DPL * l;                                           // j = i + jd + x
+    const uint8_t *pW = sW + (jd - jbase);                                  // window byte of cell (i, slot x): pW[i + x]
+    uint32_t *trl = tr + (size_t)(DPL * l) * RW;                            // trace words of slot x: trl[x * RW + (i >> 3)]
+    // rows i0 for which all DPL cells of the lane are regular inner cells (1 <= i < R, 1 <= j < e) ...
+    const int f_lo = max(NP, 1 - jd), f_hi = min(R - 1, e - 1 - jd - NP);
+    // ... and rows for which at least one cell lies inside the matrix (0 <= i <= R, 0 <= j <= e)
+    const int n_lo = max(0, -(jd + NP)), n_hi = live ? min(R + NP - 1, e - jd) : -1;
 
-    auto cell = [&](int a, int d, int diagS, int upS, int upV, int leftS, int leftH, int &S, int &H, int &V,
-                    uint32_t &acc) {
-        const int i = (a - dlo - d) >> 1, j = a - i;
-        const bool inside = (d < B) && (i >= 0) && (i <= R) && (j >= 0) && (j <= e);
-        if (!inside) { S = KT_NEG; H = KT_NEG; V = KT_NEG; return; }
-        if (i == 0) { S = 0; H = KT_NEG; V = KT_NEG; return; }                 // free first row
-        if (j == 0) { S = -(5 + i); H = KT_NEG; V = KT_NEG; return; }          // initial column (dp_formula_affine.h:291-325)
-        const int sub = (sR[i] == sW[j - jbase]) ? MATCH : MISMATCH;
+    // the recurrence of one inner cell; returns the 4 trace bits
+    auto inner = [&](int sub, int diagS, int upS, int upV, int leftS, int leftH, int &So, int &Ho, int &Vo, int &gap_o) {
         const int inter = diagS + sub;
         const int hext = leftH + GAP_EXT, hopn = leftS + GAP_OPEN;
         uint32_t code = (hext < hopn) ? 0u : 1u;             // tie -> extension
@@ -267,36 +279,99 @@ __global__ void __launch_bounds__(KB_THREADS) k1_band_kernel(const TracePlan *__
         const uint32_t gsel = (vv < hh) ? 8u : 4u;           // tie -> vertical
         const int sn = max(inter, gap);
         if (inter < gap) code |= gsel;                       // tie -> diagonal
+        So = sn; Ho = hh; Vo = vv; gap_o = gap;
+        return code;
+    };
+    // general cell: boundaries, end cell, flush on every way out of the matrix
+    auto cell = [&](int i, int x, int rb, int diagS, int upS, int upV, int leftS, int leftH, int &So, int &Ho, int &Vo) {
+        const int j = i + jd + x;
+        if ((unsigned)i > (unsigned)R || (unsigned)j > (unsigned)e) return;
+        if (i == 0 || j == 0)
+        {
+            // free first row (S = 0), initial column (dp_formula_affine.h:291-325)
+            So = (i == 0) ? 0 : -(5 + i); Ho = KT_NEG; Vo = KT_NEG;
+            return;
+        }
+        int sn, hh, vv, gap;
+        uint32_t code = inner((rb == pW[i + x]) ? MATCH : MISMATCH, diagS, upS, upV, leftS, leftH, sn, hh, vv, gap);
         if (i == R && j == e)
         {
             // end-cell correction (dp_algorithm_impl.h:1170-1185)
             if (vv == sn) code = (code & 3u) | 4u;
             else if (hh == sn) code = (code & 3u) | 8u;
         }
-        S = sn; H = hh; V = vv;
-        acc |= code << (4 * (i & 7));
-        if ((i & 7) == 7 || i == R || j == e) { tr[(size_t)d * RW + (i >> 3)] = acc; acc = 0; }
+        So = sn; Ho = hh; Vo = vv;
+        acc[x] |= code << (4 * (i & 7));
+        if ((i & 7) == 7 || i == R || j == e) { trl[x * RW + (i >> 3)] = acc[x]; acc[x] = 0; }
     };
 
-    const int nsteps = __reduce_max_sync(0xffffffffu, live ? (a_last - a_first + 2) / 2 : 0);   // step pairs
-    int a = a_first;
-    for (int it = 0; it < nsteps; ++it, a += 2)
+    for (int it = 0; it < nsteps; ++it, ++i0)
     {
-        // even-parity step: slot 0. left neighbour = lane l-1's slot 1, up neighbour = own slot 1
-        int lS = __shfl_up_sync(0xffffffffu, S1, 1, LPA);
-        int lH = __shfl_up_sync(0xffffffffu, H1, 1, LPA);
+        const bool reg_all = i0 >= f_lo && i0 <= f_hi;
+        const bool none = i0 < n_lo || i0 > n_hi;
+        const bool fast = __all_sync(0xffffffffu, reg_all || none);
+        // even step. slot 0's left neighbour = lane l-1's last slot
+        int lS = __shfl_up_sync(0xffffffffu, S[DPL - 1], 1, LPA);
+        int lH = __shfl_up_sync(0xffffffffu, H[DPL - 1], 1, LPA);
         if (l == 0) { lS = KT_NEG; lH = KT_NEG; }
+        if (fast)
         {
-            const int diagS = S0;
-            cell(a, d0, diagS, S1, V1, lS, lH, S0, H0, V0, acc0);
+            // every lane of the warp is either fully inside (inner cells only, last row excluded) or has nothing to do
+            int rbp[NP], shp[NP];
+            if (reg_all)
+            {
+#pragma unroll
+                for (int p = 0; p < NP; ++p)
+                {
+                    const int i = i0 - p, x = 2 * p;
+                    int gap;
+                    rbp[p] = sR[i]; shp[p] = 4 * (i & 7);
+                    const uint32_t code = inner((rbp[p] == pW[i + x]) ? MATCH : MISMATCH, S[x], S[x + 1], V[x + 1],
+                                                p == 0 ? lS : S[x - 1], p == 0 ? lH : H[x - 1], S[x], H[x], V[x], gap);
+                    acc[x] |= code << shp[p];
+                }
+            }
+            int uS = __shfl_down_sync(0xffffffffu, S[0], 1, LPA);
+            int uV = __shfl_down_sync(0xffffffffu, V[0], 1, LPA);
+            if (l == LPA - 1) { uS = KT_NEG; uV = KT_NEG; }
+            if (reg_all)
+            {
+#pragma unroll
+                for (int p = 0; p < NP; ++p)
+                {
+                    const int i = i0 - p, x = 2 * p + 1;
+                    int gap;
+                    const uint32_t code = inner((rbp[p] == pW[i + x]) ? MATCH : MISMATCH, S[x], p == NP - 1 ? uS : S[x + 1],
+                                                p == NP - 1 ? uV : V[x + 1], S[x - 1], H[x - 1], S[x], H[x], V[x], gap);
+                    acc[x] |= code << shp[p];
+                    if (shp[p] == 28)
+                    {
+                        uint32_t *w = trl + (i >> 3);
+                        w[(x - 1) * RW] = acc[x - 1]; w[x * RW] = acc[x];
+                        acc[x - 1] = 0; acc[x] = 0;
+                    }
+                }
+            }
+            continue;
         }
-        // odd-parity step: slot 1. up neighbour = lane l+1's slot 0, left neighbour = own slot 0
-        int uS = __shfl_down_sync(0xffffffffu, S0, 1, LPA);
-        int uV = __shfl_down_sync(0xffffffffu, V0, 1, LPA);
-        if (l == LPA - 1) { uS = KT_NEG; uV = KT_NEG; }
+        int rbp[NP];
+#pragma unroll
+        for (int p = 0; p < NP; ++p)
         {
-            const int diagS = S1;
-            cell(a + 1, d1, diagS, uS, uV, S0, H0, S1, H1, V1, acc1);
+            const int i = i0 - p, x = 2 * p;
+            rbp[p] = ((unsigned)(i - 1) < (unsigned)R) ? sR[i] : 0xFF;
+            cell(i, x, rbp[p], S[x], S[x + 1], V[x + 1], p == 0 ? lS : S[x - 1], p == 0 ? lH : H[x - 1], S[x], H[x], V[x]);
+        }
+        // odd step. the last slot's up neighbour = lane l+1's slot 0
+        int uS = __shfl_down_sync(0xffffffffu, S[0], 1, LPA);
+        int uV = __shfl_down_sync(0xffffffffu, V[0], 1, LPA);
+        if (l == LPA - 1) { uS = KT_NEG; uV = KT_NEG; }
+#pragma unroll
+        for (int p = 0; p < NP; ++p)
+        {
+            const int i = i0 - p, x = 2 * p + 1;
+            cell(i, x, rbp[p], S[x], p == NP - 1 ? uS : S[x + 1], p == NP - 1 ? uV : V[x + 1], S[x - 1], H[x - 1], S[x], H[x],
+                 V[x]);
         }
     }
 }
