@@ -181,6 +181,10 @@ def sum_over_ranks(x, world):
     return float(t.item())
 
 
+LANES_NOTE = ("the batch runs as 4 concurrent parts on the GPU (library default, svp_set_lanes); per-kernel times and "
+              "the roofline are taken in a separate single-part pass of the same steps")
+
+
 def run_gpu(args):
     import torch
     from sviper_b200 import api
@@ -208,7 +212,7 @@ def run_gpu(args):
     # L2 policy: a 256 MiB buffer (2x the 126 MB L2) is overwritten between timed steps, outside the event pairs
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     sampler = ClockSampler(local); sampler.start()
-    ctx.stats(reset=1); ctx.stats(reset=2)
+    ctx.stats(reset=1)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier(world)
     step_ms = []
@@ -221,8 +225,7 @@ def run_gpu(args):
         step_ms.append(e0.elapsed_time(e1))
     barrier(world)
     dev_ms = max_over_ranks(sum(step_ms), world)
-    n_launch, kms = ctx.stats(reset=1)
-    ctx.stats(reset=3)
+    n_launch, _ = ctx.stats(reset=1)
 
     # ---- e2e: host buffers in, results out, through the public C ABI call ----------------------
     # host buffers (the caller's reads / windows / result arrays) are laid out once, as the reference holds
@@ -240,6 +243,27 @@ def run_gpu(args):
     e2e_s = max_over_ranks(e2e_local, world)
     res_e2e = ctx.collect(pb)
     assert all(np.array_equal(a["polished"], b["polished"]) for a, b in zip(res, res_e2e))
+
+    # ---- per-kernel times: the same steps with the batch as ONE part (svp_set_lanes(1)), so that every kernel is
+    # timed without kernels of other parts running beside it. These feed `roofline` and `kernel_ms_per_step` (and
+    # are what the serialised ncu launch list under profiles/ is compared with); `value` and `e2e` above come from
+    # the default configuration, where the parts of the batch overlap.
+    ctx.set_lanes(1)
+    res1 = ctx.polish_batch(variants, with_final=True)
+    assert all(np.array_equal(a["polished"], b["polished"]) for a, b in zip(res, res1))
+    for _ in range(2):
+        ctx.polish_rerun()
+    ctx.stats(reset=1); ctx.stats(reset=2)
+    single_ms = []
+    for _ in range(args.steps):
+        flush.zero_()
+        e0.record()
+        ctx.polish_rerun()
+        e1.record()
+        torch.cuda.synchronize()
+        single_ms.append(e0.elapsed_time(e1))
+    _, kms = ctx.stats(reset=1)
+    ctx.stats(reset=3)
     sampler.stop_flag = True; sampler.join(timeout=3)
     clocks = sampler.summary()
 
@@ -267,6 +291,7 @@ def run_gpu(args):
                                    "a step = all polishing rounds + final alignment + CIGAR for the batch" % args.variants,
                        "variants_per_gpu": args.variants, "mean_rounds": float(np.mean(rounds)),
                        "alignment_gcups": tot_cells * args.steps / (dev_ms * 1e-3) / 1e9,
+                       "lanes": LANES_NOTE,
                        "l2_policy": "L2 flushed between timed steps (256 MiB buffer overwritten outside the event pairs)"},
             "e2e": {"value": tot_variants * args.steps / e2e_s, "unit": "variants/s",
                     "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
@@ -278,6 +303,8 @@ def run_gpu(args):
                          # under profiles/): the kernel is compute-bound, its DRAM traffic is negligible
                          "traffic": K1_DRAM_BYTES_PER_LAUNCH,
                          "kernel": "k1_score_kernel<19>", "kernel_ms_per_step": kms["k1_score"] / args.steps,
+                         "timed": "single-part pass of the same steps (svp_set_lanes(1)): %.3f ms per step" %
+                                  (sum(single_ms) / args.steps),
                          "peak_source": "svp_probe_dpx measured in this run: %.3e packed lane-ops/s on the 5-op "
                                         "recurrence mix (viaddmax alone %.3e, vimax3 alone %.3e)" %
                                         (probe["mix"], probe["viaddmax"], probe["vimax3"]),

@@ -176,6 +176,13 @@ int svp_probe_dpx(svp_ctx *ctx, double *viaddmax_lane_ops, double *vimax3_lane_o
  * names: k1_score, k1_trace, k2_traceback, k3_pileup_vote, k5_final, k5_traceback, pack */
 int svp_stats(svp_ctx *ctx, int32_t *n_launches, double *ms_by_kernel /* 8 entries */, int reset);
 
+/* A polish batch of >= 8 variants is split into n_lanes contiguous parts that run concurrently on the same GPU
+ * (own stream, arenas and host thread per lane), so that the latency-bound stages of one part overlap the
+ * alignment kernel of another. Results do not depend on the setting. Default 4 (environment: SVP_LANES);
+ * 1 = the whole batch as one part. The reference's counterpart is the OpenMP loop over variants
+ * (src/sviper.cpp:43-47), whose iterations are independent in the same way. */
+int svp_set_lanes(svp_ctx *ctx, int32_t n_lanes);
+
 #ifdef __cplusplus
 }
 #endif

@@ -54,7 +54,7 @@ class FinalIn(C.Structure):
 
 EXPORTS = ["svp_create", "svp_destroy", "svp_last_error", "svp_version", "svp_align_batch", "svp_align_rerun",
            "svp_polish_batch", "svp_polish_rerun", "svp_final_align_batch", "svp_assign_quality", "svp_submit_polish", "svp_wait_any",
-           "svp_debug_round", "svp_probe_dpx", "svp_stats"]
+           "svp_debug_round", "svp_probe_dpx", "svp_stats", "svp_set_lanes"]
 
 _lib = None
 
@@ -89,6 +89,7 @@ def lib():
                                       u8p, C.c_int32, i32p, f64p, u32p]
         L.svp_probe_dpx.argtypes = [C.c_void_p, f64p, f64p, f64p]
         L.svp_stats.argtypes = [C.c_void_p, i32p, f64p, C.c_int]
+        L.svp_set_lanes.argtypes = [C.c_void_p, C.c_int32]
         _lib = L
     return _lib
 
@@ -280,6 +281,10 @@ class Context:
         a, b, c = C.c_double(), C.c_double(), C.c_double()
         self._check(self.L.svp_probe_dpx(self.h, C.byref(a), C.byref(b), C.byref(c)), "svp_probe_dpx")
         return dict(viaddmax=a.value, vimax3=b.value, mix=c.value)
+
+    def set_lanes(self, n):
+        """number of concurrent parts a polish batch is split into on this GPU (svp_set_lanes)"""
+        self._check(self.L.svp_set_lanes(self.h, int(n)), "svp_set_lanes")
 
     def stats(self, reset=0):
         n = C.c_int32(); ms = (C.c_double * 8)()

@@ -3,10 +3,14 @@
 // There is deliberately no CPU implementation of any of it here (no fallback).
 #include <algorithm>
 #include <cmath>
+#include <mutex>
+#include <thread>
 #include <cfloat>
 #include <cub/device/device_scan.cuh>
 #include "ctx.cuh"
 #include "k1_score.cuh"
+
+static svp_ctx *make_ctx(int cuda_device, void *cuda_stream, bool is_lane);
 
 #include "api_align.inc"
 #include "api_polish.inc"
@@ -16,7 +20,36 @@ extern "C" {
 
 const char *svp_version(void) { return "sviper_b200 0.1 (sm_100a)"; }
 
-svp_ctx *svp_create(int cuda_device, void *cuda_stream)
+}  // extern "C"
+
+// Dynamic shared memory opt-in of the kernels that need more than 48 KB: once per device (the attribute is
+// per function and device; setting it per call would race between the lanes of a split batch).
+static int init_kernel_attrs(int device)
+{
+    static std::mutex mu;
+    static uint64_t done = 0;
+    std::lock_guard<std::mutex> lk(mu);
+    if (device < 64 && (done >> device & 1)) return SVP_OK;
+    int optin = 0;
+    if (cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device) != cudaSuccess) return SVP_ERR_CUDA;
+    auto set_max = [&](const void *fn, int want) {
+        cudaFuncAttributes fa;
+        if (cudaFuncGetAttributes(&fa, fn) != cudaSuccess) return false;
+        int room = optin - (int)fa.sharedSizeBytes;
+        return cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, want < 0 ? room : std::min(want, room)) ==
+               cudaSuccess;
+    };
+    bool ok = set_max((const void *)svp::k1_score_kernel<19>, svp::K1Shape<19>::SMEM_BYTES) &&
+              set_max((const void *)svp::k1_score_kernel<32>, svp::K1Shape<32>::SMEM_BYTES) &&
+              set_max((const void *)svp::k3_pileup_vote_kernel, -1) &&
+              set_max((const void *)svp::k5_final_kernel<true>, -1);
+    if (!ok) return SVP_ERR_CUDA;
+    if (device < 64) done |= (uint64_t)1 << device;
+    return SVP_OK;
+}
+
+// is_lane: a sub-context of a split polish batch (own stream and arenas, no lanes of its own)
+static svp_ctx *make_ctx(int cuda_device, void *cuda_stream, bool is_lane)
 {
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || cuda_device < 0 || cuda_device >= ndev)
@@ -34,8 +67,14 @@ svp_ctx *svp_create(int cuda_device, void *cuda_stream)
                 prop.major, prop.minor);
         return nullptr;
     }
+    if (init_kernel_attrs(cuda_device) != SVP_OK)
+    {
+        fprintf(stderr, "[sviper_b200] cannot opt in to large shared memory on device %d\n", cuda_device);
+        return nullptr;
+    }
     svp_ctx *ctx = new svp_ctx();
     ctx->device = cuda_device;
+    ctx->is_lane = is_lane;
     if (cuda_stream) ctx->stream = (cudaStream_t)cuda_stream;
     else
     {
@@ -45,6 +84,7 @@ svp_ctx *svp_create(int cuda_device, void *cuda_stream)
     cudaEventCreate(&ctx->ev0);
     cudaEventCreate(&ctx->ev1);
     cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&ctx->ev_call, cudaEventDisableTiming);
     for (int c = 0; c < svp::TC_N; ++c)
     {
         if (cudaStreamCreateWithFlags(&ctx->side[c], cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return nullptr; }
@@ -55,7 +95,21 @@ svp_ctx *svp_create(int cuda_device, void *cuda_stream)
     if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) ctx->arena_budget = (size_t)(free_b * 0.6);
     const char *fw = getenv("SVP_FULL_WINDOW");
     if (fw && fw[0] == '1') ctx->full_window = 1;
+    const char *ln = getenv("SVP_LANES");
+    if (ln && atoi(ln) >= 1) ctx->n_lanes = std::min(atoi(ln), SVP_MAX_LANES);
+    if (is_lane) ctx->n_lanes = 1;
     return ctx;
+}
+
+extern "C" {
+
+svp_ctx *svp_create(int cuda_device, void *cuda_stream) { return make_ctx(cuda_device, cuda_stream, false); }
+
+int svp_set_lanes(svp_ctx *ctx, int32_t n_lanes)
+{
+    if (!ctx || n_lanes < 1 || n_lanes > SVP_MAX_LANES) return SVP_ERR_ARG;
+    ctx->n_lanes = n_lanes;
+    return SVP_OK;
 }
 
 void svp_destroy(svp_ctx *ctx)
@@ -63,6 +117,8 @@ void svp_destroy(svp_ctx *ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    for (svp_ctx *l : ctx->lanes) svp_destroy(l);
+    ctx->lanes.clear();
     DevBuf *bufs[] = {&ctx->reads.bytes, &ctx->reads.w2, &ctx->reads.wn, &ctx->reads.off32, &ctx->reads.len,
                       &ctx->reads.unit_seq, &ctx->reads.byte_off, &ctx->wins.bytes, &ctx->wins.w2, &ctx->wins.wn,
                       &ctx->wins.off32, &ctx->wins.len, &ctx->wins.unit_seq, &ctx->wins.byte_off, &ctx->read_quals,
@@ -83,6 +139,7 @@ void svp_destroy(svp_ctx *ctx)
     cudaEventDestroy(ctx->ev0);
     cudaEventDestroy(ctx->ev1);
     cudaEventDestroy(ctx->ev_fork);
+    cudaEventDestroy(ctx->ev_call);
     for (int c = 0; c < svp::TC_N; ++c) { cudaEventDestroy(ctx->ev_side[c]); cudaStreamDestroy(ctx->side[c]); }
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -209,12 +266,20 @@ int svp_probe_dpx(svp_ctx *ctx, double *viaddmax_lane_ops, double *vimax3_lane_o
 int svp_stats(svp_ctx *ctx, int32_t *n_launches, double *ms_by_kernel, int reset)
 {
     if (!ctx) return SVP_ERR_ARG;
-    resolve_timers(ctx);
-    if (n_launches) *n_launches = ctx->n_launches;
-    if (ms_by_kernel) for (int i = 0; i < ST_N; ++i) ms_by_kernel[i] = ctx->ms[i];
-    if (reset == 1) { ctx->n_launches = 0; for (int i = 0; i < ST_N; ++i) ctx->ms[i] = 0; }
-    if (reset == 2) ctx->timing = true;    // enable per-kernel CUDA-event timing (events resolved lazily, no extra syncs)
-    if (reset == 3) ctx->timing = false;
+    // the lanes of a split polish batch keep their own counters: report the sums
+    std::vector<svp_ctx *> all(1, ctx);
+    all.insert(all.end(), ctx->lanes.begin(), ctx->lanes.end());
+    if (n_launches) *n_launches = 0;
+    if (ms_by_kernel) for (int i = 0; i < ST_N; ++i) ms_by_kernel[i] = 0;
+    for (svp_ctx *c : all)
+    {
+        resolve_timers(c);
+        if (n_launches) *n_launches += c->n_launches;
+        if (ms_by_kernel) for (int i = 0; i < ST_N; ++i) ms_by_kernel[i] += c->ms[i];
+        if (reset == 1) { c->n_launches = 0; for (int i = 0; i < ST_N; ++i) c->ms[i] = 0; }
+        if (reset == 2) c->timing = true;    // enable per-kernel CUDA-event timing (events resolved lazily, no extra syncs)
+        if (reset == 3) c->timing = false;
+    }
     return SVP_OK;
 }
 

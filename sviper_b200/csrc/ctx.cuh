@@ -94,6 +94,8 @@ struct DevSeqs
 struct PolishLayout;
 struct FinalSpec;
 
+constexpr int SVP_DEFAULT_LANES = 4, SVP_MAX_LANES = 16, SVP_MIN_PER_LANE = 4;
+
 struct svp_ctx
 {
     int device = 0;
@@ -103,6 +105,14 @@ struct svp_ctx
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     cudaStream_t side[svp::TC_N] = {nullptr};        // traced-pass class kernels run side by side
     cudaEvent_t ev_fork = nullptr, ev_side[svp::TC_N] = {nullptr};
+    // ---- lanes: a polish batch is split over n_lanes sub-contexts (own stream, arenas and host thread each), so that
+    // the latency-bound kernels of one lane (traced pass, traceback, vote, final alignment) overlap the score
+    // kernel of another ----
+    int n_lanes = SVP_DEFAULT_LANES;
+    bool is_lane = false;
+    std::vector<svp_ctx *> lanes;
+    std::vector<int> lane_range;            // variant ranges of the last split batch; empty: it ran on this context
+    cudaEvent_t ev_call = nullptr;          // start (parent -> lanes) / end (lane -> parent) ordering of a split call
     int n_launches = 0;
     double ms[ST_N] = {0};
     bool timing = false;

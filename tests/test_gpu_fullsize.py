@@ -111,3 +111,20 @@ def test_mixed_read_lengths_and_ns_in_one_batch(ctx):
         assert (cfg.rounds, cfg.subst, cfg.ins, cfg.del_) == (g["rounds"], g["subst"], g["ins"], g["dele"])
         sc, ops = orc.align_convex(v["ref_part"], seq)
         assert sc == g["final_score"] and orc.cigar(ops) == g["cigar"]
+
+
+def test_lanes_do_not_change_results(ctx, config1_batch):
+    """svp_set_lanes: the batch split into 1, 3 or 6 concurrent parts gives the same bits, also on a rerun"""
+    vs = config1_batch
+    try:
+        ctx.set_lanes(1)
+        base = ctx.polish_batch(vs, with_final=True)
+        for n in (3, 6, 4):
+            ctx.set_lanes(n)
+            got = ctx.polish_batch(vs, with_final=True)
+            assert all(same(a, b) for a, b in zip(base, got)), "lanes=%d" % n
+            ctx.polish_rerun()
+            n_launch, _ = ctx.stats(reset=1)
+            assert n_launch > 0
+    finally:
+        ctx.set_lanes(4)
