@@ -39,8 +39,10 @@ static int init_kernel_attrs(int device)
         return cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, want < 0 ? room : std::min(want, room)) ==
                cudaSuccess;
     };
-    bool ok = set_max((const void *)svp::k1_score_kernel<19>, svp::K1Shape<19>::SMEM_BYTES) &&
-              set_max((const void *)svp::k1_score_kernel<32>, svp::K1Shape<32>::SMEM_BYTES) &&
+    bool ok = set_max((const void *)svp::k1_score_kernel<svp::K1_G, 19>, svp::K1Shape<svp::K1_G, 19>::SMEM_BYTES) &&
+              set_max((const void *)svp::k1_score_kernel<svp::K1_G, 32>, svp::K1Shape<svp::K1_G, 32>::SMEM_BYTES) &&
+              set_max((const void *)svp::k1_score_kernel<svp::K1_GW, 5>, svp::K1Shape<svp::K1_GW, 5>::SMEM_BYTES) &&
+              set_max((const void *)svp::k1_score_kernel<svp::K1_GW, 8>, svp::K1Shape<svp::K1_GW, 8>::SMEM_BYTES) &&
               set_max((const void *)svp::k3_pileup_vote_kernel, -1) &&
               set_max((const void *)svp::k5_final_kernel<true>, -1);
     if (!ok) return SVP_ERR_CUDA;

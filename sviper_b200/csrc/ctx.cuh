@@ -210,10 +210,13 @@ __global__ void window_refresh_kernel(const VarDesc *__restrict__ descs, const V
     win_done[v] = states[v].done ? 1 : 0;
 }
 
-__global__ void count_active_kernel(const VarState *__restrict__ states, int nv, int32_t *__restrict__ out)
+// out[0] = variants still being polished, out[1] = their read pairs (an upper bound of half the live tasks)
+__global__ void count_active_kernel(const VarDesc *__restrict__ descs, const VarState *__restrict__ states, int nv,
+                                    int32_t *__restrict__ out)
 {
     int v = blockIdx.x * blockDim.x + threadIdx.x;
     int a = (v < nv) ? !states[v].done : 0;
+    if (a) atomicAdd(out + 1, descs[v].n_pairs);
     a = __syncthreads_count(a);
     if (threadIdx.x == 0 && a) atomicAdd(out, a);
 }

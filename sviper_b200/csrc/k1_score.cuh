@@ -5,7 +5,7 @@
 // and the end cell (leftmost last-row maximum, seqan/align/dp_scout.h:168-180) are concerned.
 // The traceback of the winning strand is redone by the traced pass (k1_trace.cuh).
 //
-// Mapping: 8 lanes (one "group") per (read, window) task, 4 tasks per warp. Lane g owns RPL
+// Mapping: G = 8 lanes (one "group") per (read, window) task, 4 tasks per warp (G = 32: one task per warp). Lane g owns RPL
 // consecutive read rows and sweeps the window columns as a wavefront: at step t it computes column
 // t-g and hands its bottom row (S+go, V) to lane g+1 with one shuffle pair. The low s16 half carries
 // the forward strand, the high half the reverse complement, so every DPX instruction advances two
@@ -25,28 +25,32 @@
 
 namespace svp
 {
-constexpr int K1_G = 8;                // lanes per task
-constexpr int K1_TASKS_PER_BLOCK = 16; // 128 threads
+constexpr int K1_G = 8;                // lanes per task of the throughput shape (16 tasks per 128-thread block)
+constexpr int K1_GW = 32;              // lanes per task of the WIDE shape: a third of the steps per task, more
+                                       // per-step overhead. Used when few tasks are left (tail rounds), where the
+                                       // kernel's duration is the latency of one task, not the chip's throughput.
+constexpr int K1_THREADS = 128;
 constexpr int K1_BIAS = 0x2000;
 
 __host__ __device__ constexpr uint32_t k1_pk(int x) { return (uint32_t)((K1_BIAS + x) & 0xffff) * 0x00010001u; }
 
-template <int RPL>
+template <int G, int RPL>
 struct K1Shape
 {
-    static constexpr int NSLOT = K1_G * RPL;
+    static constexpr int TASKS_PER_BLOCK = K1_THREADS / G;
+    static constexpr int NSLOT = G * RPL;
     // a lane's RPL profile entries of one window character are contiguous (fetched with LDS.128); the lane
     // stride KPAD is a multiple of 4 words with KPAD/4 odd, so the 8 lanes of a task (= one quarter-warp, the
     // conflict granularity of 128-bit loads) hit 8 distinct bank groups
     static constexpr int KPAD = ((RPL + 3) / 4 * 4) + ((((RPL + 3) / 4) & 1) ? 0 : 4);
-    static constexpr int PST = K1_G * KPAD;            // words per profile row (one window character); multiple of 32
+    static constexpr int PST = G * KPAD;               // words per profile row (one window character); multiple of 32
     static constexpr int TASK_WORDS = 5 * PST + 8;
-    static constexpr int SMEM_BYTES = K1_TASKS_PER_BLOCK * TASK_WORDS * 4;
+    static constexpr int SMEM_BYTES = TASKS_PER_BLOCK * TASK_WORDS * 4;
     static_assert(PST % 32 == 0 && TASK_WORDS % 4 == 0, "profile rows must keep bank phase and 16-byte alignment");
 };
 
-template <int RPL>
-__global__ void __launch_bounds__(128) k1_score_kernel(const int32_t *__restrict__ task_read,
+template <int G, int RPL>
+__global__ void __launch_bounds__(K1_THREADS) k1_score_kernel(const int32_t *__restrict__ task_read,
                                                        const int32_t *__restrict__ task_win,
                                                        const int32_t *__restrict__ task_idx, int ntasks,
                                                        const uint8_t *__restrict__ win_done,
@@ -56,11 +60,11 @@ __global__ void __launch_bounds__(128) k1_score_kernel(const int32_t *__restrict
                                                        ScoreOut *__restrict__ out,
                                                        uint32_t one /* always 1; opaque to the compiler */)
 {
-    using Sh = K1Shape<RPL>;
-    constexpr int G = K1_G, NSLOT = Sh::NSLOT, PST = Sh::PST, KPAD = Sh::KPAD, NQ = (RPL + 3) / 4;
+    using Sh = K1Shape<G, RPL>;
+    constexpr int NSLOT = Sh::NSLOT, PST = Sh::PST, KPAD = Sh::KPAD, NQ = (RPL + 3) / 4;
     extern __shared__ uint32_t k1_smem[];
-    const int g = threadIdx.x & (G - 1), grp = threadIdx.x >> 3;
-    const int slot = blockIdx.x * K1_TASKS_PER_BLOCK + grp;
+    const int g = threadIdx.x & (G - 1), grp = threadIdx.x / G;
+    const int slot = blockIdx.x * Sh::TASKS_PER_BLOCK + grp;
     uint32_t *prof = k1_smem + grp * Sh::TASK_WORDS;   // prof[c][g][k]
 
     int R = 0, L = 0, runit = 0, task = -1;
