@@ -129,6 +129,10 @@ typedef struct
     int32_t cigar_cap;
     int32_t n_cigar;                    /* number of CIGAR elements (assign_quality uses only this) */
     double final_score;
+    /* rounds for which the reads were re-aligned: `rounds` minus the first indel round when it follows a round
+     * that changed nothing (same consensus, same mapping; only consensus_from_profile differs, polishing.h:327-343) */
+    uint32_t alignment_rounds;
+    uint32_t reserved_;
 } svp_result;
 
 int svp_polish_batch(svp_ctx *ctx, int32_t n_variants, const svp_window_in *in, svp_result *out);

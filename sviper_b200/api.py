@@ -45,7 +45,8 @@ class Result(C.Structure):
                 ("rounds", C.c_uint32), ("substituted_bases", C.c_uint32), ("inserted_bases", C.c_uint32),
                 ("deleted_bases", C.c_uint32), ("mappQ_mean", C.c_double), ("cov_profile", u32p),
                 ("cov_cap", C.c_int32), ("cov_len", C.c_int32), ("cigar_op", C.c_char_p), ("cigar_cnt", u32p),
-                ("cigar_cap", C.c_int32), ("n_cigar", C.c_int32), ("final_score", C.c_double)]
+                ("cigar_cap", C.c_int32), ("n_cigar", C.c_int32), ("final_score", C.c_double),
+                ("alignment_rounds", C.c_uint32), ("reserved_", C.c_uint32)]
 
 
 class FinalIn(C.Structure):
@@ -223,7 +224,7 @@ class Context:
             _, pol, cov, cop, ccnt = pb["parts"][i]
             if r.status != 0:
                 raise RuntimeError("variant %d failed with status %d" % (i, r.status))
-            d = dict(polished=pol[:r.polished_len].copy(), rounds=r.rounds, subst=r.substituted_bases,
+            d = dict(polished=pol[:r.polished_len].copy(), rounds=r.rounds, alignment_rounds=r.alignment_rounds, subst=r.substituted_bases,
                      ins=r.inserted_bases, dele=r.deleted_bases, mappQ_mean=r.mappQ_mean,
                      cov=cov[:r.cov_len].copy(), n_cigar=r.n_cigar, final_score=r.final_score)
             if r.n_cigar:

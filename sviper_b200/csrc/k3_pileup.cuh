@@ -52,6 +52,8 @@ struct VarState
     double mappq_mean;
     int32_t Lp;             // view columns of the last round
     int32_t cur;            // which consensus buffer is current (0/1)
+    int32_t aligned;        // rounds that ran the alignment kernels (rounds minus the votes that reused a mapping)
+    int32_t pad_;
 };
 
 struct K3Buffers
@@ -210,7 +212,7 @@ __global__ void __launch_bounds__(K3_THREADS) k3_pileup_vote_kernel(
 
     // ---- 4. pileup + vote per reference position ---------------------------------------------
     const double qq = __dmul_rn(d.bq_mean, mappq);
-    const int fix = st.fix_indels;
+    int fix = st.fix_indels;
     unsigned n_sub = 0, n_ins = 0, n_del = 0;
     auto vote = [&](const double *c, unsigned cv, int gap, int base) -> int {
         // returns the base to emit (0..4) or 255; updates the counters
@@ -302,55 +304,85 @@ __global__ void __launch_bounds__(K3_THREADS) k3_pileup_vote_kernel(
         }
         __syncwarp();
     }
+    // A phase-1 round that changes nothing is followed by the first indel round on the SAME consensus
+    // (polishing.h:327-343): its mapping, profile and coverage are identical, only consensus_from_profile runs
+    // with fix_indels set. That round is done right here as a second vote over the stored profile (pass 1) instead
+    // of a full alignment round.
+    for (int pass = 0;; ++pass)
     {
-        typedef cub::BlockReduce<long long, K3_THREADS> BR2;
-        long long pk = ((long long)n_sub) | ((long long)n_ins << 20) | ((long long)n_del << 40);
+        if (pass == 1)
+        {
+            fix = 1; n_sub = 0; n_ins = 0; n_del = 0;
+            for (int p = tid; p < L; p += K3_THREADS)
+            {
+                const int il = inslen[p], col0 = voff[p];
+                const bool ins_in = (p > flank) && (p <= L - flank);
+                for (int k = 0; k <= il; ++k)
+                {
+                    const int col = col0 + k;
+                    double c[6];
+#pragma unroll
+                    for (int q = 0; q < 6; ++q) c[q] = profile[(size_t)col * 6 + q];
+                    if (k < il) decision[col] = ins_in ? (uint8_t)vote(c, cov[col], 1, -1) : 255;
+                    else decision[col] = (p >= flank && p < L - flank) ? (uint8_t)vote(c, cov[col], 0, cons[p]) : 255;
+                }
+            }
+        }
+        {
+            long long pk = ((long long)n_sub) | ((long long)n_ins << 20) | ((long long)n_del << 40);
+            __syncthreads();
+            pk = BR(tmp.r).Sum(pk);
+            if (tid == 0) sh_ll = pk;
+        }
         __syncthreads();
-        pk = BR(tmp.r).Sum(pk);
-        if (tid == 0) sh_ll = pk;
-    }
-    __syncthreads();
-    // ---- 5. compaction: new consensus = prefix + emitted + suffix ----------------------------
-    const int vb = voff[flank] + inslen[flank];                 // column of base `flank`
-    const int ve = voff[L - flank] + inslen[L - flank];         // column of base L - flank
-    int carry = flank;
-    for (int i = tid; i < flank; i += K3_THREADS) next[i] = cons[i];
-    for (int base = vb; base < ve; base += K3_THREADS)
-    {
-        int col = base + tid;
-        int dcs = (col < ve) ? decision[col] : 255;
-        int x = (dcs != 255), ex, tot;
-        BS(tmp.s).ExclusiveSum(x, ex, tot);
-        if (x && carry + ex < d.Lcap) next[carry + ex] = (uint8_t)dcs;
-        carry += tot;
+        // ---- 5. compaction: new consensus = prefix + emitted + suffix ----------------------------
+        const int vb = voff[flank] + inslen[flank];                 // column of base `flank`
+        const int ve = voff[L - flank] + inslen[L - flank];         // column of base L - flank
+        int carry = flank;
+        for (int i = tid; i < flank; i += K3_THREADS) next[i] = cons[i];
+        for (int base = vb; base < ve; base += K3_THREADS)
+        {
+            int col = base + tid;
+            int dcs = (col < ve) ? decision[col] : 255;
+            int x = (dcs != 255), ex, tot;
+            BS(tmp.s).ExclusiveSum(x, ex, tot);
+            if (x && carry + ex < d.Lcap) next[carry + ex] = (uint8_t)dcs;
+            carry += tot;
+            __syncthreads();
+        }
+        const int newL = carry + flank;
+        if (newL > d.Lcap) { if (tid == 0) { states[v].err = 5; states[v].done = 1; } return; }
+        for (int i = tid; i < flank; i += K3_THREADS) next[carry + i] = cons[L - flank + i];
         __syncthreads();
-    }
-    const int newL = carry + flank;
-    if (newL > d.Lcap) { if (tid == 0) { states[v].err = 5; states[v].done = 1; } return; }
-    for (int i = tid; i < flank; i += K3_THREADS) next[carry + i] = cons[L - flank + i];
-    __syncthreads();
-    // ---- 6. convergence + loop control (polishing.h:327-343) ---------------------------------
-    int diff = (newL != L);
-    if (!diff)
-        for (int i = tid; i < L; i += K3_THREADS) diff |= (next[i] != cons[i]);
-    diff = __syncthreads_or(diff);
-    if (tid == 0)
-    {
-        long long pk = sh_ll;
+        // ---- 6. convergence + loop control (polishing.h:327-343) ---------------------------------
+        int diff = (newL != L);
+        if (!diff)
+            for (int i = tid; i < L; i += K3_THREADS) diff |= (next[i] != cons[i]);
+        diff = __syncthreads_or(diff);
+        // every thread keeps its copy of the state current (pass 1 needs it), thread 0 publishes it
+        const long long pk = sh_ll;
         st.subst += (unsigned)(pk & 0xfffff); st.ins += (unsigned)((pk >> 20) & 0xfffff); st.del += (unsigned)(pk >> 40);
         st.mappq_mean = mappq;
         st.rounds += 1;
+        if (pass == 0) st.aligned += 1;
         st.Lp = Lp;
         st.L = newL;
-        st.cur ^= 1;
+        if (pass == 0) st.cur ^= 1;    // pass 1 rewrites the buffer pass 0 made current (its input is the identical old one)
+        bool again = false;
         if (force_single_round) st.done = 1;
         else if (!st.fix_indels)
         {
             if (!diff || st.rounds >= 20) st.fix_indels = 1;   // phase 2 always starts with one more round
             if (st.rounds >= 30) st.done = 1;
+            again = !diff && !st.done;
         }
         else if (!diff || st.rounds >= 30) st.done = 1;
-        states[v] = st;
+        if (!again)
+        {
+            if (tid == 0) states[v] = st;
+            break;
+        }
+        __syncthreads();
     }
 }
 }  // namespace svp

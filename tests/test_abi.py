@@ -39,7 +39,7 @@ def test_struct_layouts_match_header(lib):
     from sviper_b200 import api
     # sizes computed by hand from the header (LP64): catches accidental field drift
     assert C.sizeof(api.AlignIn) == 72 and C.sizeof(api.AlignOut) == 64
-    assert C.sizeof(api.WindowIn) == 120 and C.sizeof(api.Result) == 96 and C.sizeof(api.FinalIn) == 32
+    assert C.sizeof(api.WindowIn) == 120 and C.sizeof(api.Result) == 104 and C.sizeof(api.FinalIn) == 32
 
 
 def test_assign_quality_host_arithmetic(lib):

@@ -69,6 +69,9 @@ def test_config1_properties(ctx, config1_batch):
         f = v["flank"]
         assert np.array_equal(g["polished"][:f], v["consensus"][:f]) and np.array_equal(g["polished"][-f:], v["consensus"][-f:])
         assert 2 <= g["rounds"] <= 30 and len(g["cov"]) >= len(g["polished"]) - 1
+        # the first indel round reuses the mapping of the unchanged consensus unless phase 1 hit its round limit
+        assert g["alignment_rounds"] == g["rounds"] - (1 if g["rounds"] < 21 or g["alignment_rounds"] < g["rounds"] else 0)
+        assert g["rounds"] - 1 <= g["alignment_rounds"] <= g["rounds"]
         n_truth += int(np.array_equal(g["polished"], v["truth"]))
     assert n_truth >= 0.7 * len(vs), "polishing should recover most of the synthetic truths (%d/%d)" % (n_truth, len(vs))
     # idempotence: polishing an already polished window changes nothing (one round per phase, polishing.h:327-343)
