@@ -17,8 +17,9 @@
 // __syncthreads per step. Sequences longer than K5_THREADS*K5_RPL rows run as successive row bands with
 // the band's bottom row kept in global memory.
 // Per cell: 4 DADD (diag+sub, H+step, V+step, S+GO -- S+GO serves both the cell to the right and the cell
-// below) and 4 fp64 compares; the gap-step values travel with the gap lengths (looked up in a shared-memory
-// copy of the table when a length changes, i.e. off the S critical path).
+// below), 4 fp64 compares and 2 loads of the gap step from a shared-memory copy of the table, indexed by the
+// carried gap lengths (the kernel is bound by instruction issue, not by the latency of a step's dependency chain:
+// a load where the step is used is cheaper than carrying the value through fp64 selects).
 // Trace: 4 bits per cell as in k1_trace.cuh, one u16 per thread and step, stored anti-diagonal-major
 // (index = step * row_threads + thread) so that a warp's stores of one step are contiguous.
 #pragma once
@@ -83,12 +84,11 @@ __global__ void __launch_bounds__(K5_THREADS) k5_final_kernel(const FinalJob *__
     double *bS = bndS + job.bnd_off, *bV = bndV + job.bnd_off;
     int32_t *bVL = bndVL + job.bnd_off;
     const int nbands = job.row_threads / K5_THREADS;
-    const double g1 = tb.gapstep[1];
 
     for (int band = 0; band < nbands; ++band)
     {
         const int row0 = band * K5_BAND + T * K5_RPL;   // rows row0+1 .. row0+K5_RPL
-        double S[K5_RPL], SO[K5_RPL], H[K5_RPL], HG[K5_RPL];
+        double S[K5_RPL], SO[K5_RPL], H[K5_RPL];
         int HL[K5_RPL], sv[K5_RPL];   // HL: horizontal gap length * 8
 #pragma unroll
         for (int k = 0; k < K5_RPL; ++k)
@@ -96,7 +96,7 @@ __global__ void __launch_bounds__(K5_THREADS) k5_final_kernel(const FinalJob *__
             int row = row0 + k + 1;
             S[k] = (row <= m) ? tb.edge[row] : 0.0;
             SO[k] = __dadd_rn(S[k], GO);
-            H[k] = INF; HL[k] = 8; HG[k] = g1;
+            H[k] = INF; HL[k] = 8;
             sv[k] = (row <= m) ? job.seq[row - 1] : 255;
         }
         double prev_up = (row0 <= m) ? tb.edge[row0] : 0.0;   // S[row0][0]
@@ -113,23 +113,23 @@ __global__ void __launch_bounds__(K5_THREADS) k5_final_kernel(const FinalJob *__
             const int par = t & 1;
             if (colA >= 1 && colA <= n && live)
             {
-                double uSa, uVa, uGa, uSb, uVb, uGb; int uLa, uLb;   // uL*: vertical gap length * 8
+                double uSa, uVa, uSb, uVb; int uLa, uLb;   // uL*: vertical gap length * 8
                 if (T == 0)
                 {
                     if (band == 0)
                     {
-                        uSa = tb.edge[colA]; uSb = tb.edge[colB]; uVa = INF; uVb = INF; uLa = 8; uLb = 8; uGa = g1; uGb = g1;
+                        uSa = tb.edge[colA]; uSb = tb.edge[colB]; uVa = INF; uVb = INF; uLa = 8; uLb = 8;
                     }
                     else
                     {
-                        uSa = bS[colA]; uVa = bV[colA]; uLa = bVL[colA]; uGa = G(uLa);
-                        uSb = bS[colB]; uVb = bV[colB]; uLb = bVL[colB]; uGb = G(uLb);
+                        uSa = bS[colA]; uVa = bV[colA]; uLa = bVL[colA];
+                        uSb = bS[colB]; uVb = bV[colB]; uLb = bVL[colB];
                     }
                 }
                 else
                 {
-                    uSa = shS[par ^ 1][0][T - 1]; uVa = shV[par ^ 1][0][T - 1]; uLa = shVL[par ^ 1][0][T - 1]; uGa = G(uLa);
-                    uSb = shS[par ^ 1][1][T - 1]; uVb = shV[par ^ 1][1][T - 1]; uLb = shVL[par ^ 1][1][T - 1]; uGb = G(uLb);
+                    uSa = shS[par ^ 1][0][T - 1]; uVa = shV[par ^ 1][0][T - 1]; uLa = shVL[par ^ 1][0][T - 1];
+                    uSb = shS[par ^ 1][1][T - 1]; uVb = shV[par ^ 1][1][T - 1]; uLb = shVL[par ^ 1][1][T - 1];
                 }
                 const int hcA = job.ref[colA - 1], hcB = job.ref[colB - 1];   // ref is padded behind its end
                 double dA = prev_up;      // S(row above, A - 1)
@@ -144,17 +144,14 @@ __global__ void __launch_bounds__(K5_THREADS) k5_final_kernel(const FinalJob *__
                     // ---- column A: left neighbour = the state arrays (column A - 1)
                     const double interA = __dadd_rn(dA, (hcA == sv[k]) ? MM : MX);
                     dA = S[k];
-                    const double hgA = G(HL[k] + 8), vgA = G(uLa + 8);     // looked up before the compares resolve
-                    const double hextA = __dadd_rn(H[k], HG[k]);
+                    const double hextA = __dadd_rn(H[k], G(HL[k]));
                     const bool hxA = !(hextA < SO[k]);             // tie -> extension (dp_formula.h:152-163)
                     const double hhA = hxA ? hextA : SO[k];
                     const int hlA = hxA ? HL[k] + 8 : 8;
-                    const double hsA = hxA ? hgA : g1;
-                    const double vextA = __dadd_rn(uVa, uGa);
+                    const double vextA = __dadd_rn(uVa, G(uLa));
                     const bool vxA = !(vextA < uOa);
                     uVa = vxA ? vextA : uOa;
                     uLa = vxA ? uLa + 8 : 8;
-                    uGa = vxA ? vgA : g1;
                     const bool gvA = !(uVa < hhA);                 // tie -> vertical
                     const double gapA = gvA ? uVa : hhA;
                     const bool dgA = !(interA < gapA);             // tie -> diagonal
@@ -165,18 +162,15 @@ __global__ void __launch_bounds__(K5_THREADS) k5_final_kernel(const FinalJob *__
                     // ---- column B: left neighbour = column A of this row
                     const double interB = __dadd_rn(dB, (hcB == sv[k]) ? MM : MX);
                     dB = snA;
-                    const double hgB = G(hlA + 8), vgB = G(uLb + 8);
-                    const double hextB = __dadd_rn(hhA, hsA);
+                    const double hextB = __dadd_rn(hhA, G(hlA));
                     const bool hxB = !(hextB < uOa);
                     const double hhB = hxB ? hextB : uOa;
                     HL[k] = hxB ? hlA + 8 : 8;
-                    HG[k] = hxB ? hgB : g1;
                     H[k] = hhB;
-                    const double vextB = __dadd_rn(uVb, uGb);
+                    const double vextB = __dadd_rn(uVb, G(uLb));
                     const bool vxB = !(vextB < uOb);
                     uVb = vxB ? vextB : uOb;
                     uLb = vxB ? uLb + 8 : 8;
-                    uGb = vxB ? vgB : g1;
                     const bool gvB = !(uVb < hhB);
                     const double gapB = gvB ? uVb : hhB;
                     const bool dgB = !(interB < gapB);
