@@ -124,7 +124,7 @@ void svp_destroy(svp_ctx *ctx)
     DevBuf *bufs[] = {&ctx->reads.bytes, &ctx->reads.w2, &ctx->reads.wn, &ctx->reads.off32, &ctx->reads.len,
                       &ctx->reads.unit_seq, &ctx->reads.byte_off, &ctx->wins.bytes, &ctx->wins.w2, &ctx->wins.wn,
                       &ctx->wins.off32, &ctx->wins.len, &ctx->wins.unit_seq, &ctx->wins.byte_off, &ctx->read_quals,
-                      &ctx->qual_off, &ctx->task_read, &ctx->task_win, &ctx->task_idx19, &ctx->task_idx32,
+                      &ctx->qual_off, &ctx->task_read, &ctx->task_win, &ctx->task_mate, &ctx->win_ins, &ctx->task_idx19, &ctx->task_idx32,
                       &ctx->score_out, &ctx->plans, &ctx->units, &ctx->E, &ctx->tunits, &ctx->TE, &ctx->cls_count, &ctx->cls_list, &ctx->scan_tmp, &ctx->trace, &ctx->ops,
                       &ctx->alns, &ctx->rec_code, &ctx->rec_qual, &ctx->rec_inslen, &ctx->rec_insq, &ctx->descs,
                       &ctx->states, &ctx->pair_task, &ctx->cons0, &ctx->cons1, &ctx->inslen, &ctx->voff, &ctx->profile,

@@ -127,6 +127,8 @@ struct svp_ctx
     DevSeqs reads, wins;
     DevBuf read_quals, qual_off;            // qualities (bytes) per read, offsets
     DevBuf task_read, task_win, task_idx19, task_idx32;
+    DevBuf task_mate, win_ins;              // polish batches: mate task per task (-1 none), (insert mean, sd) per window
+    bool prune_pairs = false;               // run_trace_pass: skip the traceback of pairs that cannot be proper
     int ntasks = 0, n19 = 0, n32 = 0;
     DevBuf score_out, plans, units, E, tunits, TE, cls_count, cls_list, scan_tmp, trace, ops, alns;
     DevBuf rec_code, rec_qual, rec_inslen, rec_insq;

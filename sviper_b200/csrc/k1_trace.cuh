@@ -44,7 +44,8 @@ __global__ void plan_kernel(const int32_t *__restrict__ task_read, const int32_t
                             const int32_t *__restrict__ read_len, const ScoreOut *__restrict__ sc,
                             const uint8_t *__restrict__ win_done, TracePlan *__restrict__ plan,
                             int64_t *__restrict__ units, int64_t *__restrict__ tunits,
-                            int32_t *__restrict__ cls_count, int32_t *__restrict__ cls_list, int full_window)
+                            int32_t *__restrict__ cls_count, int32_t *__restrict__ cls_list, int full_window,
+                            const int32_t *__restrict__ task_mate, const double *__restrict__ win_ins)
 {
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= ntasks) return;
@@ -62,6 +63,47 @@ __global__ void plan_kernel(const int32_t *__restrict__ task_read, const int32_t
     p.end_col = p.is_rc ? o.col_r : o.col_f;
     int R = read_len[p.read_id];
     int slack = R - p.score; if (slack < 0) slack = 0;
+    // Pair pruning (polish batches: task_mate != null). Only proper pairs enter the pileup (polishing.h:135), and
+    // whether a pair is proper (mapping.h:168-172) can often be decided from the score pass alone: the strands,
+    // and bounds on gapsEndPos of the forward read / gapsBeginPos of the reverse one. An alignment of score s
+    // holds at most (R-s-5)/2 inserted read bases (s <= R - 2I - 5) and R-s-5 deleted columns (s <= R - 5 - D), so
+    //   endPos(F) = e_F + I_F  in [e_F, e_F + Imax_F],   beginPos(B) = e_B - R_B + I_B - D_B  in [.. - Dmax_B, .. + Imax_B].
+    // A pair that cannot be proper needs no traceback and no pileup records: only its scores are used
+    // (compute_mappQ_stats). Both mates evaluate the same predicate.
+    if (task_mate)
+    {
+        bool prune;
+        const int u = task_mate[t];
+        if (u < 0) prune = true;                               // no mate: proper_pair stays false (mapping.h:34,162)
+        else
+        {
+            const ScoreOut ou = sc[u];
+            const int u_rc = !(ou.score_f > ou.score_r);
+            if (u_rc == p.is_rc) prune = true;                 // same strand
+            else
+            {
+                const int Ru = read_len[task_read[u]];
+                const int su = u_rc ? ou.score_r : ou.score_f, eu = u_rc ? ou.col_r : ou.col_f;
+                int slu = Ru - su; if (slu < 0) slu = 0;
+                // F = forward read, B = reverse read
+                const int eF = p.is_rc ? eu : p.end_col, slF = p.is_rc ? slu : slack;
+                const int eB = p.is_rc ? p.end_col : eu, slB = p.is_rc ? slack : slu, RB = p.is_rc ? R : Ru;
+                const int ImaxF = slF > 5 ? (slF - 5) / 2 : 0, ImaxB = slB > 5 ? (slB - 5) / 2 : 0;
+                const int DmaxB = slB > 5 ? slB - 5 : 0;
+                const int dd_max = eB - RB + ImaxB - eF, dd_min = eB - RB - DmaxB - eF - ImaxF;
+                const double mean = win_ins[2 * p.win_id], sd = win_ins[2 * p.win_id + 1];
+                const double rs = fmax(0.0, mean - 3 * sd);                       // config.h:101-109
+                const double re = fmin(mean + 3 * mean, mean + 3 * sd);
+                prune = !(dd_max > rs) || !(dd_min < re);
+            }
+        }
+        if (prune)
+        {
+            p.c0 = 0; p.ncols = -2; p.band_w = -1; p.dlo = 0;
+            plan[t] = p; units[t] = 0; tunits[t] = 0;
+            return;
+        }
+    }
     int c0 = p.end_col - R - slack - 8;
     if (c0 < 0 || full_window) c0 = 0;
     p.c0 = c0; p.ncols = p.end_col - c0;
@@ -385,7 +427,7 @@ struct AlnOut
 {
     int32_t lead;      // gapsBeginPos(gapsRead)
     int32_t endpos;    // gapsEndPos(gapsRead)
-    int32_t npath;     // path ops stored (reverse order) in the ops buffer
+    int32_t npath;     // path ops stored (reverse order) in the ops buffer; -1: not traced (pair cannot be proper)
     int32_t lead_i;    // leading 'I' columns (path reached DP column 0)
     int32_t p0, n;     // records cover reference positions [p0, p0 + n)
     int32_t mapq;      // max(0, score)  (mapping.h:125,134)
@@ -419,6 +461,18 @@ __global__ void __launch_bounds__(K2_WARPS * 32) k2_traceback_kernel(
     const int t = blockIdx.x * K2_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (t >= ntasks) return;
     const TracePlan pl = plans[t];
+    if (pl.ncols == -2)
+    {
+        // pair that cannot be proper (plan_kernel): only the score is used downstream
+        if (lane == 0)
+        {
+            AlnOut o;
+            o.lead = 0; o.endpos = 0; o.npath = -1; o.lead_i = 0; o.p0 = 0; o.n = 0;
+            o.mapq = pl.score > 0 ? pl.score : 0; o.is_rc = pl.is_rc; o.err = 0;
+            out[t] = o;
+        }
+        return;
+    }
     if (pl.ncols < 0) return;   // window already converged
     const unsigned FULL = 0xffffffffu;
     const int R = reads.len[pl.read_id], L = wins.len[pl.win_id];

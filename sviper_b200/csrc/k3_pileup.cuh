@@ -130,7 +130,8 @@ __global__ void __launch_bounds__(K3_THREADS) k3_pileup_vote_kernel(
             b = alns[t2];
             aerr |= b.err;
             msum += a.mapq + b.mapq;
-            if (!a.is_rc && b.is_rc) { int dd = b.lead - a.endpos; pr = (dd > rs) && (dd < re); }
+            if (a.npath < 0 || b.npath < 0) pr = 0;     // plan_kernel proved that the pair is not proper
+            else if (!a.is_rc && b.is_rc) { int dd = b.lead - a.endpos; pr = (dd > rs) && (dd < re); }
             else if (a.is_rc && !b.is_rc) { int dd = a.lead - b.endpos; pr = (dd > rs) && (dd < re); }
         }
         else

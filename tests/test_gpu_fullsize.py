@@ -105,6 +105,21 @@ def test_mixed_read_lengths_and_ns_in_one_batch(ctx):
           synth.make_variant(53, "DEL", svlen=400, k=300, cov=6, cons_err=0.05)]
     vs[0]["reads2"][-1] = np.zeros(0, np.uint8); vs[0]["quals2"][-1] = np.zeros(0, np.uint8)
     vs[1]["ins_mean"], vs[1]["ins_sd"] = 300.0, 150.0
+    # pairs that cannot be proper (the traced pass skips them, plan_kernel): unrelated sequence, mates on the same
+    # strand, reverse-forward order, and an insert far outside mean +- 3 sd
+    rng = np.random.default_rng(5)
+    v2, q = vs[2], np.full(150, 30, np.uint8)
+    cons = v2["consensus"]
+    for _ in range(6):
+        v2["reads1"].append(rng.integers(0, 4, 150).astype(np.uint8)); v2["quals1"].append(q)
+        v2["reads2"].append(rng.integers(0, 4, 150).astype(np.uint8)); v2["quals2"].append(q)
+    a, b = cons[520:670].copy(), cons[900:1050].copy()
+    extra = [(a, b), (synth.revcomp(a), synth.revcomp(b)), (synth.revcomp(a), b), (a, synth.revcomp(cons[700:850])),
+             (cons[510:660].copy(), synth.revcomp(cons[len(cons) - 660:len(cons) - 510]))]
+    for x, y in extra:
+        v2["reads1"].append(np.ascontiguousarray(x)); v2["quals1"].append(q)
+        v2["reads2"].append(np.ascontiguousarray(y)); v2["quals2"].append(q)
+    v2["ins_mean"], v2["ins_sd"] = 120.0, 30.0
     got = ctx.polish_batch(vs, with_final=True)
     for v, g in zip(vs, got):
         r1p, r2p = rc.packed(v)
