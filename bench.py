@@ -49,6 +49,33 @@ def batch_cells(variants, rounds):
     return tot
 
 
+def make_c5_tasks(n_windows, reads_per_window, seed=5, read_len=READ_LEN):
+    """BASELINE.json configs[4] at reduced task count: window lengths from {800..2000}, every read a
+    150 bp sample of its window with 1% substitutions and 0.1% single-base indels, half reverse-complemented."""
+    rng = np.random.default_rng(seed)
+    comp = np.array([3, 2, 1, 0, 4], np.uint8)
+    lens = rng.choice([800, 1000, 1200, 1400, 1600, 1800, 2000], n_windows)
+    wins = [rng.integers(0, 4, int(L)).astype(np.uint8) for L in lens]
+    reads, tw = [], []
+    for w, win in enumerate(wins):
+        st = rng.integers(0, len(win) - read_len - 8, reads_per_window)
+        blk = win[st[:, None] + np.arange(read_len + 8)[None, :]]
+        sub = rng.random(blk.shape) < 0.01
+        blk = np.where(sub, (blk + 1 + rng.integers(0, 3, blk.shape)) % 4, blk).astype(np.uint8)
+        indel = np.nonzero(rng.random(reads_per_window) < 0.14)[0]          # ~0.1% per base over 150 bases
+        for i in indel:
+            p = int(rng.integers(1, read_len - 1))
+            r = blk[i]
+            blk[i] = np.concatenate([r[:p], r[p + 1:], r[:1]]) if rng.random() < 0.5 else \
+                np.concatenate([r[:p], rng.integers(0, 4, 1).astype(np.uint8), r[p:-1]])
+        rd = blk[:, :read_len]
+        flip = rng.random(reads_per_window) < 0.5
+        rd = np.where(flip[:, None], comp[rd[:, ::-1]], rd)
+        reads.extend(np.ascontiguousarray(x) for x in rd)
+        tw.extend([w] * reads_per_window)
+    return reads, wins, np.arange(len(reads), dtype=np.int32), np.array(tw, np.int32)
+
+
 class ClockSampler(threading.Thread):
     """samples nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)"""
 
@@ -275,6 +302,20 @@ def run_gpu(args):
     tot_cells = sum_over_ranks(cells, world)
     k1_ms = max_over_ranks(kms["k1_score"], world)
 
+    # ---- configs[4] kernel microbenchmark (score pass only, svp_align_batch / svp_align_rerun) at 1/16 scale ----
+    c5 = None
+    if rank == 0:
+        c5_reads, c5_wins, c5_tr, c5_tw = make_c5_tasks(256, 256)
+        ctx.align_batch(c5_reads, c5_wins, c5_tr, c5_tw, traceback=False)
+        c5_cells = float(sum(2 * len(c5_reads[t]) * len(c5_wins[w]) for t, w in zip(c5_tr, c5_tw)))
+        for _ in range(2):
+            ctx.align_rerun(False)
+        c5_ms = []
+        for _ in range(max(5, args.steps // 2)):
+            flush.zero_()
+            c5_ms.append(ctx.align_rerun(False))      # CUDA events around the score kernel on the library's stream
+        c5 = {"tasks": len(c5_tr), "kernel_ms": float(np.mean(c5_ms)), "gcups": c5_cells / (np.mean(c5_ms) * 1e-3) / 1e9}
+
     out = None
     if rank == 0:
         probe = ctx.probe_dpx()
@@ -312,6 +353,9 @@ def run_gpu(args):
                                         (probe["mix"], probe["viaddmax"], probe["vimax3"]),
                          "hbm_peak_gbs_measured": peaks.get("hbm_gbs")},
             "kernel_ms_per_step": {k: v / args.steps for k, v in kms.items()},
+            "alignment_microbench": dict(c5, frac_of_dpx_peak=c5["gcups"] / peak_gcups if peak_gcups else None,
+                                         workload="BASELINE.json configs[4] at 1/16 scale: 65,536 reads of 150 bp vs 256 "
+                                                  "windows of 800-2,000 bp, score pass of svp_align_batch, HBM-resident"),
         }
         # ---- cpu_baseline: the reference CPU path on this box's host cores, bounded sample -----------
         cores = host_cores()

@@ -181,7 +181,7 @@ __global__ void __launch_bounds__(K1_THREADS) k1_score_kernel(const int32_t *__r
             {
                 // strict improvement only: the leftmost maximum wins (dp_scout.h:173). Improvements are rare
                 // (a handful per task), so the per-half bookkeeping sits behind a branch.
-                if (__vmaxs2(best, __vmaxs2(uA, uB)) != best)
+                if (__vimax3_s16x2(best, uA, uB) != best)
                 {
                     uint32_t m = __vmaxs2(best, uA);
                     if ((uA & 0xffffu) > (best & 0xffffu)) colF = jj + 1;   // halves are biased positive
