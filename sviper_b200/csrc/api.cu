@@ -2,6 +2,7 @@
 // piled up, voted on or traced back is processed by the sm_100a kernels in this directory.
 // There is deliberately no CPU implementation of any of it here (no fallback).
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <mutex>
 #include <thread>
