@@ -146,3 +146,38 @@ def test_lanes_do_not_change_results(ctx, config1_batch):
             assert n_launch > 0
     finally:
         ctx.set_lanes(4)
+
+
+def test_config3_mixed_del_ins_batch(ctx):
+    """configs[2] shape (a shard of it): mixed DEL / INS of 50..1000 bp, -k 400, 30x reads; a few variants against the
+    oracle, the whole shard through the properties that do not need it"""
+    rng = np.random.default_rng(2024)
+    vs = []
+    for i in range(16):
+        kind = "DEL" if i % 2 == 0 else "INS"
+        svlen = int(np.exp(rng.uniform(np.log(50), np.log(1000))))
+        vs.append(synth.make_variant(3000 + i, kind, svlen=svlen, k=400, cov=30, cons_err=0.05))
+    got = ctx.polish_batch(vs, with_final=True)
+    for i in (1, 6, 11):                                                   # INS, DEL, INS
+        v, g = vs[i], got[i]
+        r1p, r2p = rc.packed(v)
+        cfg = rc.oracle_cfg(v, r1p, r2p)
+        seq, cov = orc.polish_to_perfection(cfg, *r1p, *r2p, v["consensus"])
+        assert np.array_equal(seq, g["polished"]) and np.array_equal(cov, g["cov"])
+        assert (cfg.rounds, cfg.subst, cfg.ins, cfg.del_) == (g["rounds"], g["subst"], g["ins"], g["dele"])
+        sc, ops = orc.align_convex(v["ref_part"], seq)
+        assert sc == g["final_score"] and orc.cigar(ops) == g["cigar"]
+    n_truth = 0
+    for v, g in zip(vs, got):
+        ref_span = sum(n for o, n in g["cigar"] if o in "MD")
+        seq_span = sum(n for o, n in g["cigar"] if o in "MI")
+        assert ref_span == len(v["ref_part"]) and seq_span == len(g["polished"])
+        # the structural variant itself shows up as the longest gap of the right kind and about the right length
+        want = "D" if v["kind"] == "DEL" else "I"
+        longest = max((n for o, n in g["cigar"] if o == want), default=0)
+        assert abs(longest - v["svlen"]) <= 0.1 * v["svlen"] + 5, (v["kind"], v["svlen"], longest)
+        n_truth += int(np.array_equal(g["polished"], v["truth"]))
+    assert n_truth >= 0.7 * len(vs)
+    # one variant at a time == the batch (different lane split, different arenas)
+    for i in (0, 5):
+        assert same(ctx.polish_batch([vs[i]], with_final=True)[0], got[i])
