@@ -208,6 +208,12 @@ def sum_over_ranks(x, world):
     return float(t.item())
 
 
+def workload_text(n):
+    return ("BASELINE.json configs[1]: %d DELs 50-1000bp per GPU, 30x 2x150bp short reads, -k 400 "
+            "(window = 500 + ~800 + 500), 5%% noisy long-read consensus, synthetic, fixed seeds; "
+            "a step = all polishing rounds + final alignment + CIGAR for the batch" % n)
+
+
 LANES_NOTE = ("the batch runs as 4 concurrent parts on the GPU (library default, svp_set_lanes); per-kernel times and "
               "the roofline are taken in a separate single-part pass of the same steps")
 
@@ -347,9 +353,7 @@ def run_gpu(args):
             "unit": "variants/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "s16x2 (alignment) + f64 (pileup, final alignment)", "data": "synthetic",
-            "config": {"workload": "BASELINE.json configs[1]: %d DELs 50-1000bp per GPU, 30x 2x150bp short reads, -k 400 "
-                                   "(window = 500 + ~800 + 500), 5%% noisy long-read consensus, synthetic, fixed seeds; "
-                                   "a step = all polishing rounds + final alignment + CIGAR for the batch" % args.variants,
+            "config": {"workload": workload_text(args.variants),
                        "variants_per_gpu": args.variants, "mean_rounds": float(np.mean(rounds)),
                        "mean_alignment_rounds": float(np.mean([r["alignment_rounds"] for r in res])),
                        "alignment_gcups": tot_cells * args.steps / (dev_ms * 1e-3) / 1e9,
@@ -418,8 +422,9 @@ def run_reference(args):
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": tot / len(times) * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32 + f64 (CPU)",
         "data": "synthetic",
-        "config": {"workload": "BASELINE.json configs[1] shape; each step = %d variants of the batch, one per host core" % n,
-                   "variants_per_gpu": args.variants},
+        "config": {"workload": workload_text(args.variants), "variants_per_gpu": args.variants,
+                   "reference_sample": "each step = the first %d variants of that batch, one per host core "
+                                       "(polish_to_perfection + final alignment of the unmodified reference)" % n},
         "cpu_baseline": {"value": val, "unit": "variants/s", "cores": used, "kind": "reference" if use_ref else "port",
                          "sample": "%d variants per step" % n},
         "e2e": {"value": val, "unit": "variants/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
