@@ -326,6 +326,8 @@ def run_gpu(args):
     tot_variants = sum_over_ranks(len(variants), world)
     tot_cells = sum_over_ranks(cells, world)
     k1_ms = max_over_ranks(kms["k1_score"], world)
+    k3_bytes = float(sum((6 * (sum(len(x) for x in v["reads1"]) + sum(len(x) for x in v["reads2"])) +
+                          57 * len(v["consensus"])) * r["alignment_rounds"] for v, r in zip(variants, res)))
 
     # ---- configs[4] kernel microbenchmark (score pass only, svp_align_batch / svp_align_rerun) at 1/16 scale ----
     c5 = None
@@ -376,6 +378,13 @@ def run_gpu(args):
                                         (probe["mix"], probe["viaddmax"], probe["vimax3"]),
                          "hbm_peak_gbs_measured": peaks.get("hbm_gbs")},
             "kernel_ms_per_step": {k: v / args.steps for k, v in kms.items()},
+            # K3 (pileup + vote): algorithmic bytes per alignment round = 6 B of records per aligned read base +
+            # 57 B per consensus column written (profile 48, coverage 4, gap flag, decision, new base, old base read);
+            # one block per variant, so the kernel is bound by per-variant latency, not by HBM
+            "pileup_kernel": {"kernel": "k3_pileup_vote_kernel", "bound": "hbm",
+                              "achieved_gbs": k3_bytes * args.steps / (kms["k3_pileup_vote"] * 1e-3) / 1e9,
+                              "peak_gbs": peaks.get("hbm_gbs"), "algorithmic_bytes_per_step": k3_bytes,
+                              "kernel_ms_per_step": kms["k3_pileup_vote"] / args.steps},
             "alignment_microbench": dict(c5, frac_of_dpx_peak=c5["gcups"] / peak_gcups if peak_gcups else None,
                                          workload="BASELINE.json configs[4] at 1/16 scale: 65,536 reads of 150 bp vs 256 "
                                                   "windows of 800-2,000 bp, score pass of svp_align_batch, HBM-resident"),

@@ -18,6 +18,7 @@
 namespace svp
 {
 constexpr int K3_THREADS = 1024;
+constexpr int K3_UNROLL = 4;      // covering alignments whose records are fetched together
 constexpr int K3_WARPS = K3_THREADS / 32;
 constexpr int K3_LIST = 512;        // per-warp list of alignments overlapping the warp's 32 positions
 
@@ -176,17 +177,35 @@ __global__ void __launch_bounds__(K3_THREADS) k3_pileup_vote_kernel(
         const int cnt = nl < 0 ? NT : nl;
         if (p < L)
         {
+            // covering alignments in chunks of K3_UNROLL: all record loads of a chunk are issued before the first
+            // use (the loop is bound by load latency, not by bandwidth); the entries are then applied in order
             int il = 0;
-            for (int x = 0; x < cnt; ++x)
+            for (int x0 = 0; x0 < cnt; x0 += K3_UNROLL)
             {
-                const int e = nl < 0 ? x : wlist[x];
-                const unsigned dd = (unsigned)(p - e_p0[e]);
-                if (dd >= (unsigned)e_n[e]) continue;
-                const int64_t r = e_roff[e] + dd;
-                const uint8_t cd = rec.code[r];
-                const int l = rec.inslen[r];
-                if (l > il) il = l;
-                if ((cd & 8u) && il < 1) il = 1;
+                bool ok[K3_UNROLL]; int64_t rr[K3_UNROLL]; uint8_t cdv[K3_UNROLL]; uint16_t ilv[K3_UNROLL];
+#pragma unroll
+                for (int u = 0; u < K3_UNROLL; ++u)
+                {
+                    const int x = x0 + u;
+                    const int e = (x < cnt) ? (nl < 0 ? x : wlist[x]) : 0;
+                    const unsigned dd = (unsigned)(p - e_p0[e]);
+                    ok[u] = (x < cnt) && dd < (unsigned)e_n[e];
+                    rr[u] = e_roff[e] + dd;
+                }
+#pragma unroll
+                for (int u = 0; u < K3_UNROLL; ++u)
+                {
+                    cdv[u] = 0; ilv[u] = 0;
+                    if (ok[u]) { cdv[u] = rec.code[rr[u]]; ilv[u] = rec.inslen[rr[u]]; }
+                }
+#pragma unroll
+                for (int u = 0; u < K3_UNROLL; ++u)
+                {
+                    if (!ok[u]) continue;
+                    const int l = ilv[u];
+                    if (l > il) il = l;
+                    if ((cdv[u] & 8u) && il < 1) il = 1;
+                }
             }
             inslen[p] = il;
         }
@@ -242,23 +261,41 @@ __global__ void __launch_bounds__(K3_THREADS) k3_pileup_vote_kernel(
             double gap0 = 0.0;
             unsigned cv = 0, noins = 0, runs = 0;
             const int il = inslen[p];
-            for (int x = 0; x < cnt; ++x)
+            for (int x0 = 0; x0 < cnt; x0 += K3_UNROLL)
             {
-                const int e = nl < 0 ? x : wlist[x];
-                const unsigned dd = (unsigned)(p - e_p0[e]);
-                if (dd >= (unsigned)e_n[e]) continue;
-                const int64_t r = e_roff[e] + dd;
-                const uint8_t cd = rec.code[r];
-                const double mq = (double)e_mapq[e];
-                const double gw = __dmul_rn(d.bq_mean, mq);
-                if (rec.inslen[r]) ++runs;
-                if (cd & 8u) { gap0 = __dadd_rn(gap0, gw); ++noins; }
-                const int sym = cd & 7u;
-                const double wgt = (sym < 5) ? __dmul_rn((double)rec.qual[r], mq) : gw;
-                // m[sym] += wgt without a dynamically indexed local array
+                bool ok[K3_UNROLL]; int64_t rr[K3_UNROLL]; int mqv[K3_UNROLL];
+                uint8_t cdv[K3_UNROLL], qv[K3_UNROLL]; uint16_t ilv[K3_UNROLL];
 #pragma unroll
-                for (int q = 0; q < 6; ++q) if (q == sym) m[q] = __dadd_rn(m[q], wgt);
-                ++cv;
+                for (int u = 0; u < K3_UNROLL; ++u)
+                {
+                    const int x = x0 + u;
+                    const int e = (x < cnt) ? (nl < 0 ? x : wlist[x]) : 0;
+                    const unsigned dd = (unsigned)(p - e_p0[e]);
+                    ok[u] = (x < cnt) && dd < (unsigned)e_n[e];
+                    rr[u] = e_roff[e] + dd; mqv[u] = e_mapq[e];
+                }
+#pragma unroll
+                for (int u = 0; u < K3_UNROLL; ++u)
+                {
+                    cdv[u] = 0; qv[u] = 0; ilv[u] = 0;
+                    if (ok[u]) { cdv[u] = rec.code[rr[u]]; qv[u] = rec.qual[rr[u]]; ilv[u] = rec.inslen[rr[u]]; }
+                }
+#pragma unroll
+                for (int u = 0; u < K3_UNROLL; ++u)
+                {
+                    if (!ok[u]) continue;                       // entries are applied in the reference's order
+                    const uint8_t cd = cdv[u];
+                    const double mq = (double)mqv[u];
+                    const double gw = __dmul_rn(d.bq_mean, mq);
+                    if (ilv[u]) ++runs;
+                    if (cd & 8u) { gap0 = __dadd_rn(gap0, gw); ++noins; }
+                    const int sym = cd & 7u;
+                    const double wgt = (sym < 5) ? __dmul_rn((double)qv[u], mq) : gw;
+                    // m[sym] += wgt without a dynamically indexed local array
+#pragma unroll
+                    for (int q = 0; q < 6; ++q) if (q == sym) m[q] = __dadd_rn(m[q], wgt);
+                    ++cv;
+                }
             }
             const int col0 = voff[p];
             const bool ins_in = (p > flank) && (p <= L - flank);
