@@ -195,6 +195,8 @@ public:
     Polisher(Polisher const &) = delete;
     Polisher & operator=(Polisher const &) = delete;
     svp_ctx * ctx() const { return ctx_; }
+    // number of concurrent parts a batch is split into on the GPU (default 4); results do not depend on it
+    void set_lanes(int n) { check(svp_set_lanes(ctx_, n), "svp_set_lanes"); }
 
     // include/sviper/polishing.h:319-346 (same argument order, same side effects on config)
     std::string polish_to_perfection(std::vector<QRead> const & reads1, std::vector<QRead> const & reads2,
