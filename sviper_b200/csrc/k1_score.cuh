@@ -50,7 +50,7 @@ struct K1Shape
 };
 
 template <int G, int RPL>
-__global__ void __launch_bounds__(K1_THREADS) k1_score_kernel(const int32_t *__restrict__ task_read,
+__global__ void __launch_bounds__(K1_THREADS, 4) k1_score_kernel(const int32_t *__restrict__ task_read,
                                                        const int32_t *__restrict__ task_win,
                                                        const int32_t *__restrict__ task_idx, int ntasks,
                                                        const uint8_t *__restrict__ win_done,
