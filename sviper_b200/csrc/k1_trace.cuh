@@ -135,7 +135,7 @@ struct KTShape
 };
 
 template <int RPL>
-__global__ void __launch_bounds__(KT_WARPS * 32) k1_trace_kernel(const TracePlan *__restrict__ plans, int ntasks,
+__global__ void __launch_bounds__(KT_WARPS * 32, 6) k1_trace_kernel(const TracePlan *__restrict__ plans, int ntasks,
                                                                 const int32_t *__restrict__ task_idx,
                                                                 SeqStore reads, SeqStore wins,
                                                                 const int64_t *__restrict__ E,
@@ -249,7 +249,7 @@ constexpr int KB_WMAX = SVP_MAX_READ_LEN + 2 * KB_MAXW32 + 8;   // staged window
 constexpr int KB_SEQ_BYTES = KB_RMAX + KB_WMAX + 8;
 
 template <int LPA, int DPL>
-__global__ void __launch_bounds__(KB_THREADS) k1_band_kernel(const TracePlan *__restrict__ plans, int ntasks,
+__global__ void __launch_bounds__(KB_THREADS, 6) k1_band_kernel(const TracePlan *__restrict__ plans, int ntasks,
                                                             const int32_t *__restrict__ task_idx, SeqStore reads,
                                                             SeqStore wins, const int64_t *__restrict__ TE,
                                                             uint32_t *__restrict__ trace)
@@ -452,7 +452,7 @@ struct RecArrays
 // is the data-parallel form of the sequential bookkeeping in add_read_to_profile (see the comments there).
 constexpr int K2_WARPS = 4;
 
-__global__ void __launch_bounds__(K2_WARPS * 32) k2_traceback_kernel(
+__global__ void __launch_bounds__(K2_WARPS * 32, 6) k2_traceback_kernel(
     const TracePlan *__restrict__ plans, int ntasks, SeqStore reads, SeqStore wins,
     const uint8_t *__restrict__ read_quals, const int64_t *__restrict__ qual_off,
     const uint32_t *__restrict__ trace, uint8_t *__restrict__ ops_buf, RecArrays rec,
