@@ -156,6 +156,40 @@ int svp_final_align_batch(svp_ctx *ctx, int32_t n, const svp_final_in *in, svp_r
 double svp_assign_quality(int32_t n_cigar, int32_t flanking_region);
 
 /* ------------------------------------------------------------------------------------------------
+ * What polish_variant does with the final CIGAR (include/sviper/sviper.h:468-489). Host arithmetic over
+ * the few dozen CIGAR elements of svp_result; together with svp_assign_quality these define the VCF
+ * fields the parity contract names: POS, END, SVLEN, SEQ, QUAL, FILTER (FAIL5).
+ * ---------------------------------------------------------------------------------------------- */
+#define SVP_SV_DEL 1   /* SV_TYPE::DEL, include/sviper/variant.h:13-21 */
+#define SVP_SV_INS 2   /* SV_TYPE::INS */
+
+typedef struct
+{
+    int32_t sv_type;       /* SVP_SV_DEL or SVP_SV_INS */
+    int32_t ref_pos;       /* Variant::ref_pos */
+    int32_t ref_pos_end;   /* Variant::ref_pos_end */
+    int32_t sv_length;     /* Variant::sv_length */
+} svp_variant_pos;
+
+/* refine_variant, coordinates (include/sviper/variant.h:277-319). begin_pos = final_record.beginPos
+ * (sviper.h:461), cigar = svp_result.cigar_op / cigar_cnt / n_cigar. Returns 1 and updates *v (and *ins_begin =
+ * offset of the inserted bases in the polished sequence, may be NULL) when the alignment still holds the variant;
+ * 0 when it was "polished away" (caller sets FILTER=FAIL5, sviper.h:474-478; *v unchanged); SVP_ERR_ARG for an
+ * unknown CIGAR operation (the reference throws) or an sv_type other than DEL / INS. */
+int svp_refine_variant(int32_t begin_pos, const char *cigar_op, const uint32_t *cigar_cnt, int32_t n_cigar,
+                       svp_variant_pos *v, int32_t *ins_begin);
+
+/* refine_variant, INFO rewrite (include/sviper/variant.h:321-349): SVLEN= / END= / SEQ= replaced where present
+ * (every occurrence, with std::regex_replace's semantics: END= also hits the tail of CIEND=), appended otherwise.
+ * *v is the refined variant, polished the polished sequence (uint8 0..4), ins_begin from svp_refine_variant
+ * (both used for insertions only). Writes at most out_cap - 1 characters + NUL; returns the full length. */
+int svp_refine_info(const char *info, const svp_variant_pos *v, const uint8_t *polished, int32_t polished_len,
+                    int32_t ins_begin, char *out, int32_t out_cap);
+
+/* QUAL as Variant::write prints it (default ostream format of a double, include/sviper/variant.h:142). */
+int svp_format_quality(double quality, char *out, int32_t out_cap);
+
+/* ------------------------------------------------------------------------------------------------
  * Batch scheduler facade (replaces the loop body at src/sviper.cpp:43-47): submissions are queued and
  * executed as one device batch on the first svp_wait_any after them. The structs (and everything they
  * point to) must stay valid until their result has been returned.

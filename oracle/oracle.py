@@ -204,3 +204,24 @@ def cigar(ops):
 
 def cigar_str(ops):
     return "".join("%d%s" % (n, o) for o, n in cigar(ops))
+
+
+def evaluate_final_mapping(sv_type, pos, end, svlen, info, cigar, polished_text, begin_pos, k):
+    """assign_quality + refine_variant (sviper.h:468-489) through the C restatement (oracle_eval.c).
+    cigar: [(op, count)], polished_text: str. Returns dict(has, pos, end, svlen, qual, filter, info)."""
+    L = lib()
+    L.orc_assign_quality.restype = C.c_double
+    ops = "".join(o for o, _ in cigar).encode()
+    cnt = (C.c_uint * max(1, len(cigar)))(*[c for _, c in cigar])
+    p, e, sl, rp = C.c_int(pos), C.c_int(end), C.c_int(svlen), C.c_int(0)
+    has = L.orc_refine_variant(C.c_int(begin_pos), ops, cnt, C.c_int(len(cigar)), C.c_int(sv_type),
+                               C.byref(p), C.byref(e), C.byref(sl), C.byref(rp))
+    out = dict(has=has, pos=p.value, end=e.value, svlen=sl.value, filter="PASS" if has == 1 else "FAIL5", info=info,
+               qual=L.orc_assign_quality(C.c_int(len(cigar)), C.c_int(k)))
+    if has == 1:
+        cap = len(info) * 8 + len(polished_text) * 4 + 256
+        buf = C.create_string_buffer(cap)
+        ins = polished_text[rp.value:rp.value + sl.value].encode() if sv_type == 2 else None
+        L.orc_refine_info(info.encode(), C.c_int(sv_type), sl, e, ins, buf, C.c_size_t(cap))
+        out["info"] = buf.value.decode()
+    return out

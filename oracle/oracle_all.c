@@ -3,6 +3,7 @@
 #include "sviper_oracle.c"
 #include "oracle_polish.c"
 #include "oracle_final.c"
+#include "oracle_eval.c"
 #ifdef _OPENMP
 #include <omp.h>
 #endif

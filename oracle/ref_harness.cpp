@@ -12,6 +12,8 @@
 //   ROUND   fix flank ins_mean ins_sd n ref  then n lines "r1 q1 r2 q2"   one polish() round with profile dump
 //   POLISH  flank ins_mean ins_sd n ref      then n lines "r1 q1 r2 q2"   polish_to_perfection (polishing.h:319)
 //   FINAL   ref_part polished              convex-gap global alignment + CIGAR (sviper.h:452-466)
+//   EVAL    type pos end svlen k begin info cigar seq   assign_quality + refine_variant on the final record
+//                                                  (sviper.h:468-489, evaluate_final_mapping.h:17-28, variant.h:277-353)
 #include <thread>
 #include <omp.h>
 #include <cstdio>
@@ -26,6 +28,8 @@
 #include <seqan/bam_io.h>
 #include <sviper/config.h>
 #include <sviper/polishing.h>
+#include <sviper/variant.h>
+#include <sviper/evaluate_final_mapping.h>
 
 using namespace seqan;
 
@@ -168,6 +172,32 @@ int main(int argc, char ** argv)
             std::cout << "FINAL score=" << hexd(s) << " ncigar=" << length(cigar) << " cigar=";
             for (unsigned i = 0; i < length(cigar); ++i) std::cout << cigar[i].count << cigar[i].operation;
             std::cout << "\n";
+        }
+        else if (cmd == "EVAL")
+        {
+            std::string type, info, cig, sq; int pos, end, svlen, k, begin;
+            in >> type >> pos >> end >> svlen >> k >> begin >> info >> cig >> sq;
+            sviper::Variant var;
+            var.sv_type = type == "DEL" ? sviper::SV_TYPE::DEL : sviper::SV_TYPE::INS;
+            var.ref_pos = pos; var.ref_pos_end = end; var.sv_length = svlen; var.info = info; var.filter = "PASS";
+            BamAlignmentRecord rec;
+            rec.beginPos = begin;
+            if (sq != "*") rec.seq = sq;
+            for (size_t i = 0; i < cig.size();)
+            {
+                unsigned c = 0;
+                while (i < cig.size() && cig[i] >= '0' && cig[i] <= '9') c = c * 10 + (cig[i++] - '0');
+                appendValue(rec.cigar, CigarElement<char, unsigned>(cig[i++], c));
+            }
+            sviper::CmdOptions opt; opt.flanking_region = k;
+            sviper::SViperConfig config{opt};
+            sviper::assign_quality(rec, var, config);
+            bool has = sviper::refine_variant(rec, var);
+            if (!has) var.filter = "FAIL5";                       // sviper.h:476-478
+            std::ostringstream qs; qs << var.quality;             // variant.h:142 (default ostream precision)
+            std::cout << "EVAL has=" << has << " pos=" << var.ref_pos << " end=" << var.ref_pos_end
+                      << " svlen=" << var.sv_length << " qual=" << hexd(var.quality) << " qualstr=" << qs.str()
+                      << " filter=" << var.filter << " info=" << var.info << "\n";
         }
         else { std::cerr << "unknown command " << cmd << "\n"; return 2; }
     }

@@ -49,13 +49,21 @@ class Result(C.Structure):
                 ("alignment_rounds", C.c_uint32), ("reserved_", C.c_uint32)]
 
 
+class VariantPos(C.Structure):
+    _fields_ = [("sv_type", C.c_int32), ("ref_pos", C.c_int32), ("ref_pos_end", C.c_int32), ("sv_length", C.c_int32)]
+
+
+SV_DEL, SV_INS = 1, 2
+
+
 class FinalIn(C.Structure):
     _fields_ = [("ref_part", u8p), ("ref_part_len", C.c_int32), ("seq", u8p), ("seq_len", C.c_int32)]
 
 
 EXPORTS = ["svp_create", "svp_destroy", "svp_last_error", "svp_version", "svp_align_batch", "svp_align_rerun",
            "svp_polish_batch", "svp_polish_rerun", "svp_final_align_batch", "svp_assign_quality", "svp_submit_polish", "svp_wait_any",
-           "svp_debug_round", "svp_probe_dpx", "svp_stats", "svp_set_lanes"]
+           "svp_debug_round", "svp_probe_dpx", "svp_stats", "svp_set_lanes", "svp_refine_variant", "svp_refine_info",
+           "svp_format_quality"]
 
 _lib = None
 
@@ -91,6 +99,9 @@ def lib():
         L.svp_probe_dpx.argtypes = [C.c_void_p, f64p, f64p, f64p]
         L.svp_stats.argtypes = [C.c_void_p, i32p, f64p, C.c_int]
         L.svp_set_lanes.argtypes = [C.c_void_p, C.c_int32]
+        L.svp_refine_variant.argtypes = [C.c_int32, C.c_char_p, u32p, C.c_int32, C.POINTER(VariantPos), i32p]
+        L.svp_refine_info.argtypes = [C.c_char_p, C.POINTER(VariantPos), u8p, C.c_int32, C.c_int32, C.c_char_p, C.c_int32]
+        L.svp_format_quality.argtypes = [C.c_double, C.c_char_p, C.c_int32]
         _lib = L
     return _lib
 
@@ -121,6 +132,38 @@ def baseq_mean(quals1, quals2):
 
 def assign_quality(n_cigar, flanking_region):
     return lib().svp_assign_quality(n_cigar, flanking_region)
+
+
+def evaluate_final_mapping(variant, cigar, polished, begin_pos, flanking_region):
+    """The tail of polish_variant (sviper.h:468-489): assign_quality + refine_variant on the final record.
+    variant: dict(sv_type=SV_DEL|SV_INS, ref_pos, ref_pos_end, sv_length, info, filter); cigar: [(op, count)] as
+    returned by Context.polish_batch; polished: uint8 bases; begin_pos = final_record.beginPos (sviper.h:461).
+    Returns a new dict with quality, quality_str, filter, ref_pos, ref_pos_end, sv_length, info."""
+    L = lib()
+    out = dict(variant)
+    out["quality"] = L.svp_assign_quality(len(cigar), flanking_region)
+    buf = C.create_string_buffer(64)
+    L.svp_format_quality(out["quality"], buf, 64)
+    out["quality_str"] = buf.value.decode()
+    ops = bytes(ord(o) if isinstance(o, str) else int(o) for o, _ in cigar)
+    cnt = np.array([c for _, c in cigar], np.uint32)
+    vp = VariantPos(variant["sv_type"], variant["ref_pos"], variant["ref_pos_end"], variant["sv_length"])
+    ins_begin = C.c_int32(0)
+    rc = L.svp_refine_variant(begin_pos, ops, _p(cnt, u32p), len(cigar), C.byref(vp), C.byref(ins_begin))
+    if rc < 0:
+        raise ValueError("svp_refine_variant: error %d (unknown CIGAR operation or SV type)" % rc)
+    if rc == 0:
+        out["filter"] = "FAIL5"
+        return out
+    pol = np.ascontiguousarray(polished, np.uint8)
+    info = variant["info"].encode()
+    need = L.svp_refine_info(info, C.byref(vp), _p(pol), len(pol), ins_begin.value, None, 0)
+    if need < 0:
+        raise ValueError("svp_refine_info: error %d" % need)
+    ibuf = C.create_string_buffer(need + 1)
+    L.svp_refine_info(info, C.byref(vp), _p(pol), len(pol), ins_begin.value, ibuf, need + 1)
+    out.update(ref_pos=vp.ref_pos, ref_pos_end=vp.ref_pos_end, sv_length=vp.sv_length, info=ibuf.value.decode())
+    return out
 
 
 STAT_NAMES = ["k1_score", "k1_trace", "k2_traceback", "k3_pileup_vote", "k5_final", "k5_traceback", "pack", "other"]

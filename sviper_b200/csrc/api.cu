@@ -16,6 +16,7 @@ static svp_ctx *make_ctx(int cuda_device, void *cuda_stream, bool is_lane);
 #include "api_align.inc"
 #include "api_polish.inc"
 #include "api_final.inc"
+#include "api_eval.inc"
 
 extern "C" {
 

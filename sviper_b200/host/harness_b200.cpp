@@ -36,9 +36,40 @@ struct PolishCase
     std::future<std::unique_ptr<ResultBuffers>> fut;
 };
 
+// EVAL lines (tests/golden/eval_cases.txt): the host arithmetic after the final alignment, no GPU involved.
+// Prints what oracle/ref_harness.cpp prints for the same line.
+static int eval_cases(char const * path)
+{
+    std::ifstream in(path);
+    if (!in) { std::cerr << "cannot open " << path << "\n"; return 2; }
+    std::string cmd;
+    while (in >> cmd)
+    {
+        if (cmd != "EVAL") { std::cerr << "unknown command " << cmd << "\n"; return 2; }
+        std::string type, cig, sq; int k, begin;
+        VariantFields var;
+        in >> type >> var.ref_pos >> var.ref_pos_end >> var.sv_length >> k >> begin >> var.info >> cig >> sq;
+        var.sv_type = type == "DEL" ? SVP_SV_DEL : SVP_SV_INS;
+        var.filter = "PASS";
+        std::vector<CigarElement> cigar;
+        for (size_t i = 0; i < cig.size();)
+        {
+            uint32_t c = 0;
+            while (i < cig.size() && cig[i] >= '0' && cig[i] <= '9') c = c * 10 + (uint32_t)(cig[i++] - '0');
+            cigar.push_back(CigarElement{cig[i++], c});
+        }
+        bool has = evaluate_final_mapping(var, cigar, sq == "*" ? "" : sq, begin, k);
+        std::cout << "EVAL has=" << has << " pos=" << var.ref_pos << " end=" << var.ref_pos_end << " svlen=" << var.sv_length
+                  << " qual=" << hexd(var.quality) << " qualstr=" << var.quality_string() << " filter=" << var.filter
+                  << " info=" << var.info << "\n";
+    }
+    return 0;
+}
+
 int main(int argc, char ** argv)
 {
-    if (argc < 2) { std::cerr << "usage: harness_b200 cases.txt [n_gpus]\n"; return 2; }
+    if (argc < 2) { std::cerr << "usage: harness_b200 cases.txt [n_gpus] | harness_b200 --eval eval_cases.txt\n"; return 2; }
+    if (std::string(argv[1]) == "--eval") return argc > 2 ? eval_cases(argv[2]) : 2;
     const int n_gpus = argc > 2 ? atoi(argv[2]) : 1;
     std::ifstream in(argv[1]);
     if (!in) { std::cerr << "cannot open " << argv[1] << "\n"; return 2; }

@@ -8,6 +8,7 @@
 //   polish_to_perfection(reads1, reads2, ref, config)  :319-346      Polisher::polish_to_perfection(r1, r2, ref, cfg)
 //   globalAlignment(..., ConvexGaps()) + getCigarString  sviper.h:457-466   Polisher::final_alignment(ref_part, polished)
 //   assign_quality(record, var, config)  evaluate_final_mapping.h:17  sviper_b200::assign_quality(n_cigar, k)
+//   assign_quality + refine_variant + FAIL5  sviper.h:468-478         sviper_b200::evaluate_final_mapping(var, cigar, polished, beginPos, k)
 //   #pragma omp parallel for over polish_variant  src/sviper.cpp:43   BatchScheduler (prepare threads -> device batches)
 //
 // No SeqAn types cross this header: sequences are std::string over "ACGTN", qualities are Phred+33 strings
@@ -98,6 +99,50 @@ inline void compute_baseQ_stats(Config & cfg, std::vector<QRead> const & reads1,
 }
 
 inline double assign_quality(int n_cigar, int flanking_region) { return svp_assign_quality(n_cigar, flanking_region); }
+
+// the Variant members the tail of polish_variant reads and writes (include/sviper/variant.h:119-131)
+struct VariantFields
+{
+    int sv_type = SVP_SV_DEL;   // SV_TYPE::DEL = 1, SV_TYPE::INS = 2 (variant.h:13-21)
+    int sv_length = -1;
+    int ref_pos = -1;
+    int ref_pos_end = -1;
+    double quality = 0;
+    std::string filter;
+    std::string info;
+    // QUAL as Variant::write prints it (variant.h:142)
+    std::string quality_string() const
+    {
+        char buf[64];
+        svp_format_quality(quality, buf, (int32_t)sizeof buf);
+        return buf;
+    }
+};
+
+// sviper.h:468-478: assign_quality, then refine_variant; FILTER becomes FAIL5 when the polished sequence no longer
+// holds the variant (var otherwise unchanged). begin_pos = final_record.beginPos (sviper.h:461), polished over "ACGTN".
+// Returns what refine_variant returns.
+inline bool evaluate_final_mapping(VariantFields & var, std::vector<CigarElement> const & cigar,
+                                   std::string const & polished, int begin_pos, int flanking_region)
+{
+    var.quality = svp_assign_quality((int32_t)cigar.size(), flanking_region);
+    std::string ops(cigar.size(), 'M');
+    std::vector<uint32_t> cnt(cigar.size());
+    for (size_t i = 0; i < cigar.size(); ++i) { ops[i] = cigar[i].operation; cnt[i] = cigar[i].count; }
+    svp_variant_pos vp = {var.sv_type, var.ref_pos, var.ref_pos_end, var.sv_length};
+    int32_t ins_begin = 0;
+    int rc = svp_refine_variant(begin_pos, ops.data(), cnt.data(), (int32_t)cigar.size(), &vp, &ins_begin);
+    if (rc < 0) throw std::logic_error("UNKNOWN CIGAR CHARACTER.");   // basics.h:169
+    if (rc == 0) { var.filter = "FAIL5"; return false; }
+    std::vector<uint8_t> pol = encode(polished);
+    int need = svp_refine_info(var.info.c_str(), &vp, pol.data(), (int32_t)pol.size(), ins_begin, nullptr, 0);
+    if (need < 0) throw std::out_of_range("inserted sequence lies outside the polished sequence");
+    std::vector<char> buf((size_t)need + 1);
+    svp_refine_info(var.info.c_str(), &vp, pol.data(), (int32_t)pol.size(), ins_begin, buf.data(), need + 1);
+    var.info.assign(buf.data(), (size_t)need);
+    var.ref_pos = vp.ref_pos; var.ref_pos_end = vp.ref_pos_end; var.sv_length = vp.sv_length;
+    return true;
+}
 
 // One variant's inputs in the C ABI's layout (owns the flattened buffers the svp_window_in points into)
 struct PackedVariant

@@ -181,3 +181,54 @@ def test_config3_mixed_del_ins_batch(ctx):
     # one variant at a time == the batch (different lane split, different arenas)
     for i in (0, 5):
         assert same(ctx.polish_batch([vs[i]], with_final=True)[0], got[i])
+
+
+def test_vcf_fields_end_to_end(ctx):
+    """POS / END / SVLEN / SEQ / QUAL / FILTER from the device CIGAR: candidate records with
+    jittered POS and SVLEN go through polish + final alignment on the GPU and the host tail
+    (svp_assign_quality / svp_refine_variant / svp_refine_info). Three variants are compared field by field with the
+    oracle run from the same inputs; all of them must recover the simulated variant; a candidate of the wrong size is
+    'polished away' (FAIL5)."""
+    from sviper_b200 import api
+    rng = np.random.default_rng(4242)
+    begin = 100000                                     # final_record.beginPos (sviper.h:461) of every window here
+    vs, cands = [], []
+    for i in range(12):
+        kind = "DEL" if i % 2 == 0 else "INS"
+        svlen = int(np.exp(rng.uniform(np.log(50), np.log(1000))))
+        v = synth.make_variant(5000 + i, kind, svlen=svlen, k=400, cov=30, cons_err=0.05)
+        true_pos = begin + v["flank"] + v["k"]
+        pos = true_pos + int(rng.integers(-10, 11))
+        cl = int(round(svlen * rng.uniform(0.9, 1.1)))
+        end = pos + cl if kind == "DEL" else pos
+        info = "SVTYPE=%s;END=%d;SVLEN=%s%d;RE=12" % (kind, end, "-" if kind == "DEL" else "", cl)
+        vs.append(v)
+        cands.append(dict(sv_type=api.SV_DEL if kind == "DEL" else api.SV_INS, ref_pos=pos, ref_pos_end=end, sv_length=cl,
+                          info=info, filter="PASS"))
+    got = ctx.polish_batch(vs, with_final=True)
+    for i, (v, c, g) in enumerate(zip(vs, cands, got)):
+        out = api.evaluate_final_mapping(c, g["cigar"], g["polished"], begin, v["k"])
+        assert out["filter"] == "PASS", (i, v["kind"], v["svlen"], g["cigar"])
+        assert out["sv_length"] == v["svlen"]
+        # random flanks can share a base or two with the variant's ends: the breakpoint may sit a few bases off
+        assert abs(out["ref_pos"] - (begin + v["flank"] + v["k"])) <= 8
+        assert out["ref_pos_end"] == (out["ref_pos"] + out["sv_length"] if v["kind"] == "DEL" else out["ref_pos"])
+        assert "SVLEN=%s%d" % ("-" if v["kind"] == "DEL" else "", v["svlen"]) in out["info"]
+        assert "END=%d" % out["ref_pos_end"] in out["info"]
+        if v["kind"] == "INS":
+            seq = out["info"].split("SEQ=")[1].split(";")[0]
+            assert len(seq) == v["svlen"]
+        assert out["quality"] == api.assign_quality(len(g["cigar"]), v["k"]) and 0.0 <= out["quality"] <= 100.0
+        if i in (0, 1, 5):                              # DEL, INS, INS through the oracle from the same inputs
+            r1p, r2p = rc.packed(v)
+            cfg = rc.oracle_cfg(v, r1p, r2p)
+            seq_o, _ = orc.polish_to_perfection(cfg, *r1p, *r2p, v["consensus"])
+            _, ops = orc.align_convex(v["ref_part"], seq_o)
+            o = orc.evaluate_final_mapping(c["sv_type"], c["ref_pos"], c["ref_pos_end"], c["sv_length"], c["info"],
+                                           orc.cigar(ops), orc.dec(seq_o), begin, v["k"])
+            assert (o["pos"], o["end"], o["svlen"], o["filter"], o["info"], o["qual"]) == \
+                (out["ref_pos"], out["ref_pos_end"], out["sv_length"], out["filter"], out["info"], out["quality"])
+        # a candidate three times the size no longer matches the polished sequence: FAIL5, fields untouched
+        wrong = dict(c, sv_length=3 * c["sv_length"] + 50)
+        bad = api.evaluate_final_mapping(wrong, g["cigar"], g["polished"], begin, v["k"])
+        assert bad["filter"] == "FAIL5" and bad["info"] == c["info"] and bad["ref_pos"] == c["ref_pos"]

@@ -22,6 +22,15 @@ def test_driver_builds():
     assert os.path.exists(BIN)
 
 
+def test_cpp_evaluate_final_mapping_matches_reference_fixture():
+    """POS / END / SVLEN / SEQ / QUAL / FAIL5 through polisher.hpp's evaluate_final_mapping (host arithmetic of the
+    C ABI, no GPU): identical text to what the unmodified reference printed (tests/golden/eval_expected.txt)"""
+    subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "sviper_b200", "csrc"), "../host/harness_b200"])
+    out = subprocess.check_output([BIN, "--eval", os.path.join(G, "eval_cases.txt")], text=True)
+    assert out == open(os.path.join(G, "eval_expected.txt")).read()
+    assert out.count("\n") == 330
+
+
 @pytest.mark.gpu
 def test_cpp_host_matches_reference_fixture():
     """the same case file through the reference harness (committed expected.txt) and through the C++ host
