@@ -190,6 +190,36 @@ int svp_refine_info(const char *info, const svp_variant_pos *v, const uint8_t *p
 int svp_format_quality(double quality, char *out, int32_t out_cap);
 
 /* ------------------------------------------------------------------------------------------------
+ * What polish_variant does with BAM records BEFORE the hot path. Host arithmetic over
+ * (op, count) CIGAR arrays, no SeqAn types; reading the BAM / FASTA files stays the reference's own code.
+ * ---------------------------------------------------------------------------------------------- */
+/* record_supports_variant (include/sviper/variant.h:239-275, called for every long read at sviper.h:236-249):
+ * 1 if the record's CIGAR holds a D (DEL) / I (INS) element of 0.4..1.6 x sv_length inside
+ * [ref_pos - sv_length/2, ref_pos + 1.5 x sv_length], else 0 (also for any other sv_type); SVP_ERR_ARG for an unknown
+ * CIGAR operation (the reference throws std::logic_error). */
+int svp_record_supports_variant(int32_t begin_pos, const char *cigar_op, const uint32_t *cigar_cnt, int32_t n_cigar,
+                                const svp_variant_pos *v);
+
+/* get_read_region_boundaries (include/sviper/basics.h:189-241, the long-read crop of sviper.h:318-340): the read
+ * positions that correspond to the reference region [ref_region_begin, ref_region_end) under the record's CIGAR.
+ * Returns 0; 1 with (0, 0) when begin >= end (the reference prints a message and returns (0, 0)); SVP_ERR_ARG for an
+ * unknown operation or a region that ends before the record starts (the reference reads cigar[-1] there). */
+int svp_read_region_boundaries(int32_t begin_pos, const char *cigar_op, const uint32_t *cigar_cnt, int32_t n_cigar,
+                               int32_t ref_region_begin, int32_t ref_region_end, int32_t *read_region_begin,
+                               int32_t *read_region_end);
+
+/* seqan::getAlignmentLengthInRef (extern/seqan/include/seqan/bam_io/cigar.h:598-610): everything but S, H, I. */
+int32_t svp_alignment_length_in_ref(const char *cigar_op, const uint32_t *cigar_cnt, int32_t n_cigar);
+
+/* cut_down_high_coverage (include/sviper/basics.h:403-442, sviper.h:405): the short-read records of a region, sorted by
+ * (position ascending, mapping quality descending) and thinned so that no more than mean_coverage kept reads start
+ * while that many are still open. keep[] (capacity n) receives the indices of the kept records in output order;
+ * returns their number, or SVP_ERR_ARG where the reference would run out of its `ends` array (a record that reaches
+ * beyond the last record's end + 500, or a gap of more than 32,767 bases). */
+int svp_cut_down_high_coverage(int32_t n, const int32_t *begin_pos, const uint8_t *mapq, const int32_t *len_in_ref,
+                               int32_t mean_coverage, int32_t *keep);
+
+/* ------------------------------------------------------------------------------------------------
  * Batch scheduler facade (replaces the loop body at src/sviper.cpp:43-47): submissions are queued and
  * executed as one device batch on the first svp_wait_any after them. The structs (and everything they
  * point to) must stay valid until their result has been returned.

@@ -14,6 +14,9 @@
 //   FINAL   ref_part polished              convex-gap global alignment + CIGAR (sviper.h:452-466)
 //   EVAL    type pos end svlen k begin info cigar seq   assign_quality + refine_variant on the final record
 //                                                  (sviper.h:468-489, evaluate_final_mapping.h:17-28, variant.h:277-353)
+//   SUPPORT type pos svlen begin cigar         record_supports_variant on a long-read record (variant.h:239-275)
+//   REGION  begin cigar ref_begin ref_end      get_read_region_boundaries (basics.h:189-241)
+//   CUTCOV  cov n  then n lines "name begin mapq cigar"   cut_down_high_coverage (basics.h:403-442)
 #include <thread>
 #include <omp.h>
 #include <cstdio>
@@ -28,6 +31,7 @@
 #include <seqan/bam_io.h>
 #include <sviper/config.h>
 #include <sviper/polishing.h>
+#include <sviper/basics.h>
 #include <sviper/variant.h>
 #include <sviper/evaluate_final_mapping.h>
 
@@ -70,6 +74,16 @@ static void read_pairs(std::istream & in, unsigned n, StringSet<Dna5QString> & r
         in >> a >> qa >> b >> qb;
         appendValue(r1, mkread(a, qa));
         appendValue(r2, mkread(b, qb));
+    }
+}
+
+static void parse_cigar(std::string const & cig, String<CigarElement<char, unsigned>> & out)
+{
+    for (size_t i = 0; i < cig.size();)
+    {
+        unsigned c = 0;
+        while (i < cig.size() && cig[i] >= '0' && cig[i] <= '9') c = c * 10 + (cig[i++] - '0');
+        appendValue(out, CigarElement<char, unsigned>(cig[i++], c));
     }
 }
 
@@ -198,6 +212,46 @@ int main(int argc, char ** argv)
             std::cout << "EVAL has=" << has << " pos=" << var.ref_pos << " end=" << var.ref_pos_end
                       << " svlen=" << var.sv_length << " qual=" << hexd(var.quality) << " qualstr=" << qs.str()
                       << " filter=" << var.filter << " info=" << var.info << "\n";
+        }
+        else if (cmd == "SUPPORT")
+        {
+            std::string type, cig; int pos, svlen, begin;
+            in >> type >> pos >> svlen >> begin >> cig;
+            sviper::Variant var;
+            var.sv_type = type == "DEL" ? sviper::SV_TYPE::DEL : sviper::SV_TYPE::INS;
+            var.ref_pos = pos; var.sv_length = svlen;
+            var.ref_pos_end = type == "DEL" ? pos + svlen : pos;
+            BamAlignmentRecord rec;
+            rec.beginPos = begin;
+            parse_cigar(cig, rec.cigar);
+            std::cout << "SUPPORT supports=" << sviper::record_supports_variant(rec, var) << "\n";
+        }
+        else if (cmd == "REGION")
+        {
+            std::string cig; int begin, rb, re;
+            in >> begin >> cig >> rb >> re;
+            BamAlignmentRecord rec;
+            rec.beginPos = begin; rec.qName = "r";
+            parse_cigar(cig, rec.cigar);
+            auto t = sviper::get_read_region_boundaries(rec, rb, re);
+            std::cout << "REGION begin=" << std::get<0>(t) << " end=" << std::get<1>(t) << "\n";
+        }
+        else if (cmd == "CUTCOV")
+        {
+            int cov; unsigned n;
+            in >> cov >> n;
+            std::vector<BamAlignmentRecord> recs(n);
+            for (unsigned i = 0; i < n; ++i)
+            {
+                std::string name, cig; int begin, mq;
+                in >> name >> begin >> mq >> cig;
+                recs[i].qName = name; recs[i].beginPos = begin; recs[i].mapQ = mq;
+                parse_cigar(cig, recs[i].cigar);
+            }
+            sviper::cut_down_high_coverage(recs, (int16_t)cov);
+            std::cout << "CUTCOV n=" << recs.size() << " keep=";
+            for (size_t i = 0; i < recs.size(); ++i) std::cout << (i ? "," : "") << recs[i].qName;
+            std::cout << "\n";
         }
         else { std::cerr << "unknown command " << cmd << "\n"; return 2; }
     }

@@ -63,7 +63,8 @@ class FinalIn(C.Structure):
 EXPORTS = ["svp_create", "svp_destroy", "svp_last_error", "svp_version", "svp_align_batch", "svp_align_rerun",
            "svp_polish_batch", "svp_polish_rerun", "svp_final_align_batch", "svp_assign_quality", "svp_submit_polish", "svp_wait_any",
            "svp_debug_round", "svp_probe_dpx", "svp_stats", "svp_set_lanes", "svp_refine_variant", "svp_refine_info",
-           "svp_format_quality"]
+           "svp_format_quality", "svp_record_supports_variant", "svp_read_region_boundaries",
+           "svp_alignment_length_in_ref", "svp_cut_down_high_coverage"]
 
 _lib = None
 
@@ -102,6 +103,10 @@ def lib():
         L.svp_refine_variant.argtypes = [C.c_int32, C.c_char_p, u32p, C.c_int32, C.POINTER(VariantPos), i32p]
         L.svp_refine_info.argtypes = [C.c_char_p, C.POINTER(VariantPos), u8p, C.c_int32, C.c_int32, C.c_char_p, C.c_int32]
         L.svp_format_quality.argtypes = [C.c_double, C.c_char_p, C.c_int32]
+        L.svp_record_supports_variant.argtypes = [C.c_int32, C.c_char_p, u32p, C.c_int32, C.POINTER(VariantPos)]
+        L.svp_read_region_boundaries.argtypes = [C.c_int32, C.c_char_p, u32p, C.c_int32, C.c_int32, C.c_int32, i32p, i32p]
+        L.svp_alignment_length_in_ref.argtypes = [C.c_char_p, u32p, C.c_int32]
+        L.svp_cut_down_high_coverage.argtypes = [C.c_int32, i32p, u8p, i32p, C.c_int32, i32p]
         _lib = L
     return _lib
 
@@ -164,6 +169,50 @@ def evaluate_final_mapping(variant, cigar, polished, begin_pos, flanking_region)
     L.svp_refine_info(info, C.byref(vp), _p(pol), len(pol), ins_begin.value, ibuf, need + 1)
     out.update(ref_pos=vp.ref_pos, ref_pos_end=vp.ref_pos_end, sv_length=vp.sv_length, info=ibuf.value.decode())
     return out
+
+
+def _cigar_arrays(cigar):
+    ops = bytes(ord(o) if isinstance(o, str) else int(o) for o, _ in cigar)
+    return ops, np.array([c for _, c in cigar], np.uint32)
+
+
+def record_supports_variant(begin_pos, cigar, sv_type, ref_pos, sv_length):
+    """record_supports_variant (variant.h:239-275) for one long-read record; cigar: [(op, count)]"""
+    ops, cnt = _cigar_arrays(cigar)
+    vp = VariantPos(sv_type, ref_pos, ref_pos + sv_length if sv_type == SV_DEL else ref_pos, sv_length)
+    rc = lib().svp_record_supports_variant(begin_pos, ops, _p(cnt, u32p), len(cigar), C.byref(vp))
+    if rc < 0:
+        raise ValueError("UNKNOWN CIGAR CHARACTER.")
+    return bool(rc)
+
+
+def get_read_region_boundaries(begin_pos, cigar, ref_region_begin, ref_region_end):
+    """get_read_region_boundaries (basics.h:189-241): (read_begin, read_end) of a reference region"""
+    ops, cnt = _cigar_arrays(cigar)
+    b, e = C.c_int32(0), C.c_int32(0)
+    rc = lib().svp_read_region_boundaries(begin_pos, ops, _p(cnt, u32p), len(cigar), ref_region_begin, ref_region_end,
+                                          C.byref(b), C.byref(e))
+    if rc < 0:
+        raise ValueError("svp_read_region_boundaries: unknown CIGAR operation, or the region ends before the record")
+    return b.value, e.value
+
+
+def cut_down_high_coverage(records, mean_coverage):
+    """cut_down_high_coverage (basics.h:403-442); records: [dict(begin_pos, mapq, cigar)] -> the kept ones, in the
+    reference's output order"""
+    L = lib()
+    n = len(records)
+    bp = np.array([r["begin_pos"] for r in records], np.int32)
+    mq = np.array([r["mapq"] for r in records], np.uint8)
+    ln = np.zeros(n, np.int32)
+    for i, r in enumerate(records):
+        ops, cnt = _cigar_arrays(r["cigar"])
+        ln[i] = L.svp_alignment_length_in_ref(ops, _p(cnt, u32p), len(r["cigar"]))
+    keep = np.zeros(max(1, n), np.int32)
+    k = L.svp_cut_down_high_coverage(n, _p(bp, i32p), _p(mq), _p(ln, i32p), mean_coverage, _p(keep, i32p))
+    if k < 0:
+        raise ValueError("svp_cut_down_high_coverage: error %d" % k)
+    return [records[i] for i in keep[:k]]
 
 
 STAT_NAMES = ["k1_score", "k1_trace", "k2_traceback", "k3_pileup_vote", "k5_final", "k5_traceback", "pack", "other"]

@@ -13,6 +13,7 @@
 #include <sstream>
 
 #include "polisher.hpp"
+#include "prepare.hpp"
 
 using namespace sviper_b200;
 
@@ -66,10 +67,72 @@ static int eval_cases(char const * path)
     return 0;
 }
 
+static std::vector<CigarElement> parse_cigar(std::string const & cig)
+{
+    std::vector<CigarElement> cigar;
+    for (size_t i = 0; i < cig.size();)
+    {
+        uint32_t c = 0;
+        while (i < cig.size() && cig[i] >= '0' && cig[i] <= '9') c = c * 10 + (uint32_t)(cig[i++] - '0');
+        cigar.push_back(CigarElement{cig[i++], c});
+    }
+    return cigar;
+}
+
+// SUPPORT / REGION / CUTCOV lines (tests/golden/prep_cases.txt): the CIGAR walks before the hot path, no GPU involved.
+// Prints what oracle/ref_harness.cpp prints for the same lines.
+static int prep_cases(char const * path)
+{
+    std::ifstream in(path);
+    if (!in) { std::cerr << "cannot open " << path << "\n"; return 2; }
+    std::string cmd;
+    while (in >> cmd)
+    {
+        if (cmd == "SUPPORT")
+        {
+            std::string type, cig; AlignedRecord rec; VariantFields var;
+            in >> type >> var.ref_pos >> var.sv_length >> rec.beginPos >> cig;
+            var.sv_type = type == "DEL" ? SVP_SV_DEL : SVP_SV_INS;
+            var.ref_pos_end = type == "DEL" ? var.ref_pos + var.sv_length : var.ref_pos;
+            rec.cigar = parse_cigar(cig);
+            std::cout << "SUPPORT supports=" << record_supports_variant(rec, var) << "\n";
+        }
+        else if (cmd == "REGION")
+        {
+            std::string cig; AlignedRecord rec; int rb, re;
+            in >> rec.beginPos >> cig >> rb >> re;
+            rec.qName = "r";
+            rec.cigar = parse_cigar(cig);
+            auto t = get_read_region_boundaries(rec, rb, re);
+            std::cout << "REGION begin=" << std::get<0>(t) << " end=" << std::get<1>(t) << "\n";
+        }
+        else if (cmd == "CUTCOV")
+        {
+            int cov; unsigned n;
+            in >> cov >> n;
+            std::vector<AlignedRecord> recs(n);
+            for (unsigned i = 0; i < n; ++i)
+            {
+                std::string cig; int mq;
+                in >> recs[i].qName >> recs[i].beginPos >> mq >> cig;
+                recs[i].mapQ = (uint8_t)mq;
+                recs[i].cigar = parse_cigar(cig);
+            }
+            cut_down_high_coverage(recs, (int16_t)cov);
+            std::cout << "CUTCOV n=" << recs.size() << " keep=";
+            for (size_t i = 0; i < recs.size(); ++i) std::cout << (i ? "," : "") << recs[i].qName;
+            std::cout << "\n";
+        }
+        else { std::cerr << "unknown command " << cmd << "\n"; return 2; }
+    }
+    return 0;
+}
+
 int main(int argc, char ** argv)
 {
-    if (argc < 2) { std::cerr << "usage: harness_b200 cases.txt [n_gpus] | harness_b200 --eval eval_cases.txt\n"; return 2; }
+    if (argc < 2) { std::cerr << "usage: harness_b200 cases.txt [n_gpus] | harness_b200 --eval eval_cases.txt | harness_b200 --prep prep_cases.txt\n"; return 2; }
     if (std::string(argv[1]) == "--eval") return argc > 2 ? eval_cases(argv[2]) : 2;
+    if (std::string(argv[1]) == "--prep") return argc > 2 ? prep_cases(argv[2]) : 2;
     const int n_gpus = argc > 2 ? atoi(argv[2]) : 1;
     std::ifstream in(argv[1]);
     if (!in) { std::cerr << "cannot open " << argv[1] << "\n"; return 2; }
