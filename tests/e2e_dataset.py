@@ -41,8 +41,8 @@ def make(outdir, seed=1, contig_len=60000, cov_short=30, cov_long=20, k=400, onl
     os.makedirs(outdir, exist_ok=True)
     ref = rng.integers(0, 4, contig_len).astype(np.uint8)
     # (type, 0-based ref position of the first affected base / insertion point, length)
-    svs = [("DEL", 6000, 100), ("INS", 13000, 300), ("DEL", 20000, 300), ("INS", 27000, 100), ("DEL", 34000, 800),
-           ("INS", 42000, 800)]
+    lens = [100, 300, 300, 100, 800, 800]
+    svs = [("DEL" if i % 2 == 0 else "INS", 6000 + 7000 * i, lens[i % 6]) for i in range(max(0, (contig_len - 18000) // 7000))]
     # ---- the sample's haplotype, with for every alt base the reference coordinate it maps to -----------------
     alt, amap, akind = [], [], []          # akind: 0 = reference base, 1 = inserted base
     p = 0
@@ -111,7 +111,7 @@ def make(outdir, seed=1, contig_len=60000, cov_short=30, cov_long=20, k=400, onl
     # ---- short reads: fragments of the haplotype, both mates placed at their reference coordinate -----------
     recs = []
     n_pairs = int(cov_short * len(alt) / 300)
-    lo_gap, hi_gap = 55000, 57500                                           # almost no short reads here: FAIL4
+    lo_gap, hi_gap = contig_len - 5000, contig_len - 2500                                           # almost no short reads here: FAIL4
     for i in range(n_pairs):
         fl = int(np.clip(rng.normal(430, 40), 320, 700))
         st = int(rng.integers(0, len(alt) - fl))
@@ -149,12 +149,12 @@ def make(outdir, seed=1, contig_len=60000, cov_short=30, cov_long=20, k=400, onl
             end = jp + jl if typ == "DEL" else jp
             info = "SVTYPE=%s;END=%d;SVLEN=%s%d" % (typ, end, "-" if typ == "DEL" else "", jl)
             f.write("chr1\t%d\tsv%d\tN\t<%s>\t.\tPASS\t%s\tGT\t1/1\n" % (jp, n, typ, info)); n += 1
-        f.write("chr1\t46000\tsv%d\tN\t<DUP>\t.\tPASS\tSVTYPE=DUP;END=46500;SVLEN=500\tGT\t0/1\n" % n); n += 1      # SKIP
-        f.write("chr1\t48000\tsv%d\tN\t<DEL>\t.\tPASS\tSVTYPE=DEL;END=48200;SVLEN=-200\tGT\t0/1\n" % n); n += 1      # FAIL2
-        f.write("chr1\t56000\tsv%d\tN\t<DEL>\t.\tPASS\tSVTYPE=DEL;END=56200;SVLEN=-200\tGT\t0/1\n" % n); n += 1      # FAIL1
+        f.write("chr1\t%d\tsv%d\tN\t<DUP>\t.\tPASS\tSVTYPE=DUP;END=%d;SVLEN=500\tGT\t0/1\n" % (contig_len - 14000, n, contig_len - 13500)); n += 1   # SKIP
+        f.write("chr1\t%d\tsv%d\tN\t<DEL>\t.\tPASS\tSVTYPE=DEL;END=%d;SVLEN=-200\tGT\t0/1\n" % (contig_len - 12000, n, contig_len - 11800)); n += 1   # FAIL2
+        f.write("chr1\t%d\tsv%d\tN\t<DEL>\t.\tPASS\tSVTYPE=DEL;END=%d;SVLEN=-200\tGT\t0/1\n" % (contig_len - 4000, n, contig_len - 3800)); n += 1   # FAIL1
         f.write("chr2\t1000\tsv%d\tN\t<DEL>\t.\tPASS\tSVTYPE=DEL;END=1200;SVLEN=-200\tGT\t0/1\n" % n); n += 1         # FAIL0
     return dict(ref=fa, vcf=vcf, long=os.path.join(outdir, "long.bam"), short=os.path.join(outdir, "short.bam"), k=k,
-                n_records=n)
+                n_records=n, n_sv=0 if only_filter_paths else len(svs))
 
 
 if __name__ == "__main__":
