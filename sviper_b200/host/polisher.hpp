@@ -14,6 +14,7 @@
 // No SeqAn types cross this header: sequences are std::string over "ACGTN", qualities are Phred+33 strings
 // (what seqan::Dna5QString prints). Everything is computed by the CUDA library; a failed call throws.
 #pragma once
+#include <chrono>
 #include <condition_variable>
 #include <cstdint>
 #include <cstring>
@@ -303,8 +304,10 @@ public:
         std::promise<std::unique_ptr<ResultBuffers>> done;
     };
 
-    BatchScheduler(std::vector<int> const & cuda_devices, size_t max_batch = 256)
-        : max_batch_(max_batch ? max_batch : 1)
+    // linger_us: after the first submission arrives a worker waits this long for more before it forms the batch
+    // (submitters that block on their future, like the OpenMP threads of the GPU build, arrive one by one)
+    BatchScheduler(std::vector<int> const & cuda_devices, size_t max_batch = 256, unsigned linger_us = 0)
+        : max_batch_(max_batch ? max_batch : 1), linger_us_(linger_us)
     {
         for (int dev : cuda_devices) polishers_.emplace_back(new Polisher(dev));
         for (size_t g = 0; g < polishers_.size(); ++g) workers_.emplace_back([this, g] { run(g); });
@@ -331,7 +334,7 @@ public:
             std::lock_guard<std::mutex> lk(m_);
             queue_.push_back(std::move(j));
         }
-        cv_.notify_one();
+        cv_.notify_all();   // a lingering worker must not swallow the wake-up of an idle one
         return f;
     }
     size_t n_gpus() const { return polishers_.size(); }
@@ -346,10 +349,13 @@ private:
                 std::unique_lock<std::mutex> lk(m_);
                 cv_.wait(lk, [this] { return stop_ || !queue_.empty(); });
                 if (queue_.empty()) return;   // stop requested and nothing left
+                if (linger_us_ && !stop_)
+                    cv_.wait_for(lk, std::chrono::microseconds(linger_us_), [this] { return stop_ || queue_.size() >= max_batch_; });
                 // leave work for the other GPUs: take at most an even share of what is queued
                 size_t take = (queue_.size() + polishers_.size() - 1) / polishers_.size();
                 if (take > max_batch_) take = max_batch_;
                 for (size_t i = 0; i < take; ++i) { batch.push_back(std::move(queue_.front())); queue_.erase(queue_.begin()); }
+                if (!queue_.empty()) cv_.notify_all();
             }
             std::vector<PackedVariant *> in;
             std::vector<ResultBuffers *> out;
@@ -367,6 +373,7 @@ private:
     }
 
     size_t max_batch_;
+    unsigned linger_us_;
     std::vector<std::unique_ptr<Polisher>> polishers_;
     std::vector<std::thread> workers_;
     std::vector<std::unique_ptr<Job>> queue_;

@@ -53,7 +53,9 @@ inline std::vector<int> devices()
 
 inline BatchScheduler & scheduler()
 {
-    static BatchScheduler s(devices());
+    // SVIPER_B200_LINGER_US (default 500): how long a device worker waits for further OpenMP threads to arrive
+    char const * e = std::getenv("SVIPER_B200_LINGER_US");
+    static BatchScheduler s(devices(), 256, e ? (unsigned)std::atoi(e) : 500u);
     return s;
 }
 

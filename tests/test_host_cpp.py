@@ -45,3 +45,19 @@ def test_cpp_host_matches_reference_fixture():
         assert o == e
         n += 1
     assert n == 64
+
+
+def test_gpu_build_of_reference_program_routes_the_hot_path_to_the_library():
+    """sviper_b200_cli = the reference's unmodified src/sviper.cpp compiled with host/shim in front of its include path:
+    its only imports from the library are the two hot-path entry points, and SeqAn's convex-gap DP (the final alignment
+    of sviper.h:457-460) is not instantiated any more, i.e. the overload in the shim was chosen."""
+    cli = os.path.join(HOST, "sviper_b200_cli")
+    if not os.path.exists(cli):
+        pytest.skip("sviper_b200_cli not built (needs the reference tree at build time)")
+    syms = subprocess.check_output(["nm", "-C", cli], text=True)
+    imports = sorted(set(line.split()[-1] for line in syms.split("\n") if " U svp_" in line))
+    assert "svp_polish_batch" in imports and "svp_final_align_batch" in imports
+    assert "onvex" not in syms
+    ref = os.path.join(ROOT, "oracle", "_ref", "sviper")
+    if os.path.exists(ref):
+        assert "onvex" in subprocess.check_output(["nm", "-C", ref], text=True)     # the reference does instantiate it
