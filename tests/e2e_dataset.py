@@ -1,7 +1,7 @@
 """Synthetic end-to-end inputs of SURVEY.md section 8(d) config C1 (the reference ships no test data,
 tests/sviper_test.sh only prints the help page): one contig, homozygous DELs and INSs, 30x 2x150 short reads,
 20x noisy long reads whose CIGARs hold the SV as one D / I element, and a candidate VCF with jittered POS / SVLEN
-plus records that take the FILTER paths (SKIP, FAIL0, FAIL1, FAIL2). Written as FASTA + .fai, two coordinate-sorted
+plus records that take the FILTER paths (SKIP, FAIL0, FAIL1, FAIL2, FAIL4). Written as FASTA + .fai, two coordinate-sorted
 BAM + BAI files (tests/bamwriter.py) and a VCF.
 
 Used by tests/test_e2e_vcf.py to run the UNMODIFIED reference binary and the GPU build on the same files.
@@ -43,6 +43,7 @@ def make(outdir, seed=1, contig_len=60000, cov_short=30, cov_long=20, k=400, onl
     # (type, 0-based ref position of the first affected base / insertion point, length)
     lens = [100, 300, 300, 100, 800, 800]
     svs = [("DEL" if i % 2 == 0 else "INS", 6000 + 7000 * i, lens[i % 6]) for i in range(max(0, (contig_len - 18000) // 7000))]
+    svs.append(("DEL", contig_len - 8000, 200))          # supported by long reads, but (almost) no short reads there: FAIL4
     # ---- the sample's haplotype, with for every alt base the reference coordinate it maps to -----------------
     alt, amap, akind = [], [], []          # akind: 0 = reference base, 1 = inserted base
     p = 0
@@ -67,12 +68,12 @@ def make(outdir, seed=1, contig_len=60000, cov_short=30, cov_long=20, k=400, onl
         f.write("chr1\t%d\t6\t60\t61\n" % contig_len)
 
     # ---- long reads: 8-15 kb of the haplotype, 10% errors, true CIGAR against the reference ------------------
-    # no long read starts inside the last 9 kb (FAIL1 record there), none covers [49,000, 51,000) with the SV
+    # no long read reaches into the last 3.5 kb (FAIL1 record there)
     recs = []
     n_long = int(cov_long * len(alt) / 11500)
     for i in range(n_long):
         ln = int(rng.integers(8000, 15001))
-        st = int(rng.integers(0, max(1, len(alt) - 9000 - ln)))
+        st = int(rng.integers(0, max(1, len(alt) - 3500 - ln)))
         ops, opref, bases = [], [], []          # opref: reference coordinate of an M / D op (None for I)
         prev_ref = None
         u_all = rng.random(ln); nb_all = rng.integers(0, 4, (ln, 2))
@@ -111,7 +112,7 @@ def make(outdir, seed=1, contig_len=60000, cov_short=30, cov_long=20, k=400, onl
     # ---- short reads: fragments of the haplotype, both mates placed at their reference coordinate -----------
     recs = []
     n_pairs = int(cov_short * len(alt) / 300)
-    lo_gap, hi_gap = contig_len - 5000, contig_len - 2500                                           # almost no short reads here: FAIL4
+    lo_gap, hi_gap = contig_len - 9500, contig_len - 6500                                           # almost no short reads here: FAIL4
     for i in range(n_pairs):
         fl = int(np.clip(rng.normal(430, 40), 320, 700))
         st = int(rng.integers(0, len(alt) - fl))
@@ -143,7 +144,7 @@ def make(outdir, seed=1, contig_len=60000, cov_short=30, cov_long=20, k=400, onl
         f.write('##FORMAT=<ID=GT,Number=1,Type=String,Description="Genotype">\n')
         f.write("#CHROM\tPOS\tID\tREF\tALT\tQUAL\tFILTER\tINFO\tFORMAT\tSAMPLE\n")
         n = 0
-        for typ, pos, ln in ([] if only_filter_paths else svs):
+        for typ, pos, ln in (svs[-1:] if only_filter_paths else svs):
             jp = pos + int(rng.integers(-10, 11))
             jl = max(30, int(ln * rng.uniform(0.9, 1.1)))
             end = jp + jl if typ == "DEL" else jp
@@ -151,10 +152,10 @@ def make(outdir, seed=1, contig_len=60000, cov_short=30, cov_long=20, k=400, onl
             f.write("chr1\t%d\tsv%d\tN\t<%s>\t.\tPASS\t%s\tGT\t1/1\n" % (jp, n, typ, info)); n += 1
         f.write("chr1\t%d\tsv%d\tN\t<DUP>\t.\tPASS\tSVTYPE=DUP;END=%d;SVLEN=500\tGT\t0/1\n" % (contig_len - 14000, n, contig_len - 13500)); n += 1   # SKIP
         f.write("chr1\t%d\tsv%d\tN\t<DEL>\t.\tPASS\tSVTYPE=DEL;END=%d;SVLEN=-200\tGT\t0/1\n" % (contig_len - 12000, n, contig_len - 11800)); n += 1   # FAIL2
-        f.write("chr1\t%d\tsv%d\tN\t<DEL>\t.\tPASS\tSVTYPE=DEL;END=%d;SVLEN=-200\tGT\t0/1\n" % (contig_len - 4000, n, contig_len - 3800)); n += 1   # FAIL1
+        f.write("chr1\t%d\tsv%d\tN\t<DEL>\t.\tPASS\tSVTYPE=DEL;END=%d;SVLEN=-200\tGT\t0/1\n" % (contig_len - 2000, n, contig_len - 1800)); n += 1   # FAIL1
         f.write("chr2\t1000\tsv%d\tN\t<DEL>\t.\tPASS\tSVTYPE=DEL;END=1200;SVLEN=-200\tGT\t0/1\n" % n); n += 1         # FAIL0
     return dict(ref=fa, vcf=vcf, long=os.path.join(outdir, "long.bam"), short=os.path.join(outdir, "short.bam"), k=k,
-                n_records=n, n_sv=0 if only_filter_paths else len(svs))
+                n_records=n, n_sv=0 if only_filter_paths else len(svs) - 1)
 
 
 if __name__ == "__main__":
