@@ -30,7 +30,9 @@ def test_bam_writer_is_read_by_the_reference(tmp_path):
 
 def hot_path_lines(log):
     keep = []
-    for line in open(log):
+    with open(log) as f:
+        lines = f.readlines()
+    for line in lines:
         if line.startswith(("DONE POLISHING", "SUCCESS", "ERROR", "--- Built a consensus", "--- Extracted",
                             "--- Short read base qualities")) or (line[:1].isdigit() and " " in line):
             keep.append(line)
@@ -40,7 +42,9 @@ def hot_path_lines(log):
 def variant_blocks(log):
     """per-variant blocks of a sviper log, keyed by the variant id"""
     blocks, cur = {}, None
-    for line in open(log):
+    with open(log) as f:
+        lines = f.readlines()
+    for line in lines:
         if line.startswith(" PROCESS Variant "):
             cur = line.split()[2]
             blocks[cur] = []

@@ -32,7 +32,7 @@ def main():
     tmp = tempfile.mkdtemp(prefix="svp_cli_")
     d = e2e_dataset.make(tmp, seed=11, contig_len=a.contig)
     common = ["-c", d["vcf"], "-l", d["long"], "-s", d["short"], "-r", d["ref"], "-k", str(d["k"]), "-t", str(a.threads)]
-    out = {"workload": "tests/e2e_dataset.py contig %d bp: %d DEL/INS of 100-800 bp + 4 FILTER-path records, 30x short / "
+    out = {"workload": "tests/e2e_dataset.py contig %d bp: %d DEL/INS of 100-800 bp + 5 FILTER-path records, 30x short / "
                        "20x long reads, -k 400" % (a.contig, d["n_sv"]), "threads": a.threads, "records": d["n_records"]}
     for name, binary in (("reference_cpu", REF_BIN), ("gpu_build", GPU_BIN)):
         best = None
