@@ -219,6 +219,30 @@ int32_t svp_alignment_length_in_ref(const char *cigar_op, const uint32_t *cigar_
 int svp_cut_down_high_coverage(int32_t n, const int32_t *begin_pos, const uint8_t *mapq, const int32_t *len_in_ref,
                                int32_t mean_coverage, int32_t *keep);
 
+/* merge_record_group (include/sviper/merge_split_alignments.h:378-534; merge_alignments, :536-561, calls it once per read
+ * name, sviper.h:262-266): the supplementary alignments of a read are folded into its primary alignment, so that a split
+ * long read shows the DEL / INS as one CIGAR element. recs = all records of ONE read name in input order. *chosen = index
+ * of the record the result is based on (first after the reference's sort: primary first, then by mapping quality; its
+ * flag / mapQ / name carry over), begin_pos / cigar / seq = the merged alignment. SVP_ERR_ARG for an unknown CIGAR
+ * operation or where the reference indexes out of bounds (empty CIGAR, clip longer than the other record's sequence);
+ * SVP_ERR_CAPACITY if the output buffers are too small (n_cigar / seq_len then hold the needed sizes). */
+typedef struct
+{
+    int32_t begin_pos;          /* BamAlignmentRecord::beginPos (0-based) */
+    int32_t rid;                /* rID */
+    uint16_t flag;              /* BAM flag: 0x10 reverse, 0x100 secondary, 0x800 supplementary */
+    uint8_t mapq;
+    const char *cigar_op;
+    const uint32_t *cigar_cnt;
+    int32_t n_cigar;
+    const char *seq;            /* as stored in the record (hard-clipped bases absent) */
+    int32_t seq_len;
+} svp_bam_record;
+
+int svp_merge_record_group(int32_t n, const svp_bam_record *recs, int32_t *chosen, int32_t *begin_pos, char *cigar_op,
+                           uint32_t *cigar_cnt, int32_t cigar_cap, int32_t *n_cigar, char *seq, int32_t seq_cap,
+                           int32_t *seq_len);
+
 /* ------------------------------------------------------------------------------------------------
  * Batch scheduler facade (replaces the loop body at src/sviper.cpp:43-47): submissions are queued and
  * executed as one device batch on the first svp_wait_any after them. The structs (and everything they

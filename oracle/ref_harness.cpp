@@ -17,6 +17,8 @@
 //   SUPPORT type pos svlen begin cigar         record_supports_variant on a long-read record (variant.h:239-275)
 //   REGION  begin cigar ref_begin ref_end      get_read_region_boundaries (basics.h:189-241)
 //   CUTCOV  cov n  then n lines "name begin mapq cigar"   cut_down_high_coverage (basics.h:403-442)
+//   MERGE   n  then n lines "name flag rid begin mapq cigar seq" (sorted by name)   merge_alignments
+//                                                  (merge_split_alignments.h:378-561, called at sviper.h:266)
 #include <thread>
 #include <omp.h>
 #include <cstdio>
@@ -33,6 +35,7 @@
 #include <sviper/polishing.h>
 #include <sviper/basics.h>
 #include <sviper/variant.h>
+#include <sviper/merge_split_alignments.h>
 #include <sviper/evaluate_final_mapping.h>
 
 using namespace seqan;
@@ -251,6 +254,29 @@ int main(int argc, char ** argv)
             sviper::cut_down_high_coverage(recs, (int16_t)cov);
             std::cout << "CUTCOV n=" << recs.size() << " keep=";
             for (size_t i = 0; i < recs.size(); ++i) std::cout << (i ? "," : "") << recs[i].qName;
+            std::cout << "\n";
+        }
+        else if (cmd == "MERGE")
+        {
+            unsigned n;
+            in >> n;
+            std::vector<BamAlignmentRecord> recs(n);
+            for (unsigned i = 0; i < n; ++i)
+            {
+                std::string name, cig, sq; int flag, rid, begin, mq;
+                in >> name >> flag >> rid >> begin >> mq >> cig >> sq;
+                recs[i].qName = name; recs[i].flag = flag; recs[i].rID = rid; recs[i].beginPos = begin; recs[i].mapQ = mq;
+                parse_cigar(cig, recs[i].cigar);
+                recs[i].seq = sq;
+            }
+            std::vector<BamAlignmentRecord> out = sviper::merge_alignments(recs);
+            std::cout << "MERGE n=" << out.size();
+            for (auto const & r : out)
+            {
+                std::cout << " " << r.qName << ":" << r.flag << ":" << r.beginPos << ":" << (int)r.mapQ << ":";
+                for (unsigned i = 0; i < length(r.cigar); ++i) std::cout << r.cigar[i].count << r.cigar[i].operation;
+                std::cout << ":" << r.seq;
+            }
             std::cout << "\n";
         }
         else { std::cerr << "unknown command " << cmd << "\n"; return 2; }

@@ -56,6 +56,12 @@ class VariantPos(C.Structure):
 SV_DEL, SV_INS = 1, 2
 
 
+class BamRecord(C.Structure):
+    _fields_ = [("begin_pos", C.c_int32), ("rid", C.c_int32), ("flag", C.c_uint16), ("mapq", C.c_uint8),
+                ("cigar_op", C.c_char_p), ("cigar_cnt", C.POINTER(C.c_uint32)), ("n_cigar", C.c_int32),
+                ("seq", C.c_char_p), ("seq_len", C.c_int32)]
+
+
 class FinalIn(C.Structure):
     _fields_ = [("ref_part", u8p), ("ref_part_len", C.c_int32), ("seq", u8p), ("seq_len", C.c_int32)]
 
@@ -64,7 +70,7 @@ EXPORTS = ["svp_create", "svp_destroy", "svp_last_error", "svp_version", "svp_al
            "svp_polish_batch", "svp_polish_rerun", "svp_final_align_batch", "svp_assign_quality", "svp_submit_polish", "svp_wait_any",
            "svp_debug_round", "svp_probe_dpx", "svp_stats", "svp_set_lanes", "svp_refine_variant", "svp_refine_info",
            "svp_format_quality", "svp_record_supports_variant", "svp_read_region_boundaries",
-           "svp_alignment_length_in_ref", "svp_cut_down_high_coverage"]
+           "svp_alignment_length_in_ref", "svp_cut_down_high_coverage", "svp_merge_record_group"]
 
 _lib = None
 
@@ -107,6 +113,8 @@ def lib():
         L.svp_read_region_boundaries.argtypes = [C.c_int32, C.c_char_p, u32p, C.c_int32, C.c_int32, C.c_int32, i32p, i32p]
         L.svp_alignment_length_in_ref.argtypes = [C.c_char_p, u32p, C.c_int32]
         L.svp_cut_down_high_coverage.argtypes = [C.c_int32, i32p, u8p, i32p, C.c_int32, i32p]
+        L.svp_merge_record_group.argtypes = [C.c_int32, C.POINTER(BamRecord), i32p, i32p, C.c_char_p, u32p, C.c_int32, i32p,
+                                             C.c_char_p, C.c_int32, i32p]
         _lib = L
     return _lib
 
@@ -213,6 +221,38 @@ def cut_down_high_coverage(records, mean_coverage):
     if k < 0:
         raise ValueError("svp_cut_down_high_coverage: error %d" % k)
     return [records[i] for i in keep[:k]]
+
+
+def merge_alignments(records):
+    """merge_alignments (merge_split_alignments.h:536-561); records: [dict(name, flag, rid, begin_pos, mapq, cigar, seq)]
+    sorted by name -> one merged record per name (the reference's output order)"""
+    L = lib()
+    out, b = [], 0
+    while b < len(records):
+        e = b + 1
+        while e < len(records) and records[e]["name"] == records[b]["name"]:
+            e += 1
+        grp = records[b:e]
+        keep, arr = [], (BamRecord * len(grp))()
+        for i, r in enumerate(grp):
+            ops, cnt = _cigar_arrays(r["cigar"])
+            sq = r["seq"].encode()
+            keep.append((ops, cnt, sq))
+            arr[i] = BamRecord(r["begin_pos"], r["rid"], r["flag"], r["mapq"], ops, _p(cnt, u32p), len(cnt), sq, len(sq))
+        ccap = sum(len(r["cigar"]) + 2 for r in grp) + 16
+        scap = sum(len(r["seq"]) for r in grp) + 16
+        oop, ocnt, oseq = C.create_string_buffer(ccap), np.zeros(ccap, np.uint32), C.create_string_buffer(scap)
+        chosen, begin, ncig, slen = C.c_int32(), C.c_int32(), C.c_int32(), C.c_int32()
+        rc = L.svp_merge_record_group(len(grp), arr, C.byref(chosen), C.byref(begin), oop, _p(ocnt, u32p), ccap,
+                                      C.byref(ncig), oseq, scap, C.byref(slen))
+        if rc != 0:
+            raise ValueError("svp_merge_record_group: error %d (the reference indexes out of bounds on this group)" % rc)
+        m = dict(grp[chosen.value])
+        m.update(begin_pos=begin.value, cigar=[(chr(oop.raw[i]), int(ocnt[i])) for i in range(ncig.value)],
+                 seq=oseq.raw[:slen.value].decode())
+        out.append(m)
+        b = e
+    return out
 
 
 STAT_NAMES = ["k1_score", "k1_trace", "k2_traceback", "k3_pileup_vote", "k5_final", "k5_traceback", "pack", "other"]

@@ -18,6 +18,7 @@ static svp_ctx *make_ctx(int cuda_device, void *cuda_stream, bool is_lane);
 #include "api_final.inc"
 #include "api_eval.inc"
 #include "api_prepare.inc"
+#include "api_merge.inc"
 
 extern "C" {
 

@@ -123,6 +123,30 @@ static int prep_cases(char const * path)
             for (size_t i = 0; i < recs.size(); ++i) std::cout << (i ? "," : "") << recs[i].qName;
             std::cout << "\n";
         }
+        else if (cmd == "MERGE")
+        {
+            unsigned n;
+            in >> n;
+            std::vector<AlignedRecord> recs(n);
+            for (unsigned i = 0; i < n; ++i)
+            {
+                std::string cig; int flag, mq;
+                in >> recs[i].qName >> flag >> recs[i].rID >> recs[i].beginPos >> mq >> cig >> recs[i].seq;
+                recs[i].flag = (uint16_t)flag; recs[i].mapQ = (uint8_t)mq;
+                recs[i].cigar = parse_cigar(cig);
+            }
+            std::vector<AlignedRecord> out;
+            try { out = merge_alignments(recs); }
+            catch (std::logic_error const &) { std::cout << "MERGE undefined\n"; continue; }   // out-of-bounds access in the reference
+            std::cout << "MERGE n=" << out.size();
+            for (AlignedRecord const & r : out)
+            {
+                std::cout << " " << r.qName << ":" << r.flag << ":" << r.beginPos << ":" << (int)r.mapQ << ":";
+                for (CigarElement const & e : r.cigar) std::cout << e.count << e.operation;
+                std::cout << ":" << r.seq;
+            }
+            std::cout << "\n";
+        }
         else { std::cerr << "unknown command " << cmd << "\n"; return 2; }
     }
     return 0;

@@ -1,5 +1,5 @@
 """The CIGAR walks of polish_variant's prepare side: record_supports_variant
-(variant.h:239-275), get_read_region_boundaries (basics.h:189-241), cut_down_high_coverage (basics.h:403-442).
+(variant.h:239-275), get_read_region_boundaries (basics.h:189-241), cut_down_high_coverage (basics.h:403-442), merge_alignments (merge_split_alignments.h:378-561).
 tests/golden/prep_expected.txt holds what the UNMODIFIED reference printed for prep_cases.txt (make_golden_prep.py).
 Checked against it: the product's C ABI through ctypes, and the C++ host mirror (sviper_b200/host/prepare.hpp) through
 harness_b200 --prep. Host arithmetic, no GPU needed."""
@@ -94,6 +94,67 @@ def test_c_abi_errors():
         api.cut_down_high_coverage(far, 10)
     assert api.cut_down_high_coverage([], 10) == []
     assert L.svp_alignment_length_in_ref(b"SMIDMH", api._p(np.array([5, 10, 2, 3, 7, 4], np.uint32), api.u32p), 6) == 20
+
+
+# ---- merge_alignments (merge_split_alignments.h:378-561): tests/golden/merge_*.txt ---------------------------------
+def read_merge_cases(path):
+    cases = []
+    with open(path) as f:
+        lines = iter(f.read().split("\n"))
+    for line in lines:
+        p = line.split()
+        if not p:
+            continue
+        assert p[0] == "MERGE"
+        recs = []
+        for _ in range(int(p[1])):
+            q = next(lines).split()
+            recs.append(dict(name=q[0], flag=int(q[1]), rid=int(q[2]), begin_pos=int(q[3]), mapq=int(q[4]), cigar=cigar(q[5]),
+                             seq=q[6]))
+        cases.append(recs)
+    return cases
+
+
+def merge_line(recs):
+    out = api.merge_alignments(recs)
+    return "MERGE n=%d " % len(out) + " ".join("%s:%d:%d:%d:%s:%s" % (
+        r["name"], r["flag"], r["begin_pos"], r["mapq"], "".join("%d%s" % (c, o) for o, c in r["cigar"]), r["seq"]) for r in out)
+
+
+def test_merge_alignments_c_abi_matches_reference():
+    cases = read_merge_cases(os.path.join(G, "merge_cases.txt"))
+    exp = open(os.path.join(G, "merge_expected.txt")).read().strip("\n").split("\n")
+    assert len(cases) == len(exp) >= 100
+    for recs, e in zip(cases, exp):
+        assert merge_line(recs) == e
+    # most groups really are merged: the expected line holds a D / I element that no input record has
+    inputs_have = lambda recs, el: any(el in [(o, c) for o, c in r["cigar"]] for r in recs)
+    n_new = 0
+    for recs, e in zip(cases, exp):
+        for tok in e.split()[2:]:
+            big = [(o, c) for o, c in cigar(tok.split(":")[4]) if o in "DI" and c >= 20]
+            n_new += any(not inputs_have(recs, el) for el in big)
+    assert n_new >= 60
+
+
+def test_merge_alignments_cpp_host_matches_reference():
+    subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "sviper_b200", "csrc"), "../host/harness_b200"])
+    out = subprocess.check_output([BIN, "--prep", os.path.join(G, "merge_cases.txt")], text=True)
+    assert out == open(os.path.join(G, "merge_expected.txt")).read()
+
+
+def test_merge_alignments_refuses_what_is_undefined_in_the_reference():
+    """a primary whose 500 hard-clipped bases would have to come from a supplementary record that only holds 100: the
+    reference copies prefix(seq, 500) beyond the sequence (heap garbage in its output, seen while generating the
+    fixture); the C ABI answers SVP_ERR_ARG"""
+    recs = [dict(name="r", flag=0, rid=0, begin_pos=5000, mapq=60, cigar=[("H", 500), ("M", 300)], seq="A" * 300),
+            dict(name="r", flag=2048, rid=0, begin_pos=4000, mapq=60, cigar=[("M", 100), ("H", 700)], seq="C" * 100)]
+    with pytest.raises(ValueError):
+        api.merge_alignments(recs)
+    recs[1]["seq"] = "C" * 100
+    recs[1]["cigar"] = [("N", 100)]                                      # unknown operation: the reference throws
+    with pytest.raises(ValueError):
+        api.merge_alignments(recs)
 
 
 @pytest.mark.skipif(not os.path.exists(rc.HARNESS), reason="reference harness not built")
