@@ -310,6 +310,7 @@ def run_gpu(args):
     for _ in range(2):
         ctx.polish_rerun()
     ctx.stats(reset=1); ctx.stats(reset=2)
+    ctx.k1_cells(reset=1)
     single_ms = []
     for _ in range(args.steps):
         flush.zero_()
@@ -319,6 +320,8 @@ def run_gpu(args):
         torch.cuda.synchronize()
         single_ms.append(e0.elapsed_time(e1))
     _, kms = ctx.stats(reset=1)
+    k1_reg_cells, k1_mix_cells = ctx.k1_cells(reset=1, split=True)   # cells the score kernel computed in the per-kernel pass
+    k1_computed = k1_reg_cells + k1_mix_cells
     ctx.stats(reset=3)
     sampler.stop_flag = True; sampler.join(timeout=3)
     clocks = sampler.summary()
@@ -328,7 +331,6 @@ def run_gpu(args):
     d2h = sum(len(r["polished"]) + 4 * len(r["cov"]) + 5 * r["n_cigar"] + 64 for r in res)
     tot_variants = sum_over_ranks(len(variants), world)
     tot_cells = sum_over_ranks(cells, world)
-    k1_ms = max_over_ranks(kms["k1_score"], world)
     k3_bytes = float(sum((6 * (sum(len(x) for x in v["reads1"]) + sum(len(x) for x in v["reads2"])) +
                           57 * len(v["consensus"])) * r["alignment_rounds"] for v, r in zip(variants, res)))
 
@@ -351,7 +353,11 @@ def run_gpu(args):
         probe = ctx.probe_dpx()
         # peak cells/s of the 5-instruction packed recurrence (IADD, 2x VIADDMNMX, VIMNMX3, IADD; 2 cells each)
         peak_gcups = probe["mix"] / 5.0 * 2.0 / 1e9
-        k1_gcups = cells * args.steps / (kms["k1_score"] * 1e-3) / 1e9
+        # roofline = the dominant kernel, k1_score_kernel<8,19,regular>: the full-batch rounds that align both strands of
+        # every read (cells COMPUTED over their own time). Rounds >= 2 run a pair's two known strands as one packed task
+        # (half the cells, less than one wave of blocks at 100 variants: latency-bound) and are reported beside it;
+        # config.alignment_gcups is the algorithmic figure (2 x |read| x |window| per read and round) over the whole step.
+        k1_gcups = k1_reg_cells / (kms["k1_score"] * 1e-3) / 1e9
         # pileup/vote kernel: HBM-bound; algorithmic bytes = records read + profile/cov/decision written
         out = {
             "metric": "variants_polished_per_sec", "value": tot_variants * args.steps / (dev_ms * 1e-3),
@@ -376,6 +382,13 @@ def run_gpu(args):
                          # under profiles/): the kernel is compute-bound, its DRAM traffic is negligible
                          "traffic": K1_DRAM_BYTES_PER_LAUNCH,
                          "kernel": "k1_score_kernel<19>", "kernel_ms_per_step": kms["k1_score"] / args.steps,
+                         "cells_computed_per_step": k1_reg_cells / args.steps,
+                         "mixed_rounds": {"what": "score pass of rounds >= 2: pairs with certified strands as one packed task "
+                                                  "(k1_score_kernel<.,.,mixed>) + the remaining regular tasks",
+                                          "ms_per_step": kms["k1_score_mixed"] / args.steps,
+                                          "cells_computed_per_step": k1_mix_cells / args.steps,
+                                          "gcups": (k1_mix_cells / (kms["k1_score_mixed"] * 1e-3) / 1e9) if kms["k1_score_mixed"] else None},
+                         "score_pass_cells_computed_over_algorithmic": k1_computed / float(cells * args.steps) if cells else None,
                          "timed": "single-part pass of the same steps (svp_set_lanes(1)): %.3f ms per step" %
                                   (sum(single_ms) / args.steps),
                          "peak_source": "svp_probe_dpx measured in this run: %.3e packed lane-ops/s on the 5-op "

@@ -260,13 +260,19 @@ int svp_debug_round(svp_ctx *ctx, const svp_window_in *w, int fix_indels, double
                     uint8_t *isgap, int32_t cap_cols, int32_t *n_cols, uint8_t *proper, uint8_t *out_seq,
                     int32_t out_cap, int32_t *out_len, double *mappQ_mean, uint32_t *counters /* subst, ins, del */);
 
+/* DP cells the score kernel has computed for polish batches on this context since the last reset (both halves of every
+ * packed lane count): cells[0] in regular rounds (both strands of every read, the reference's 2 x |read| x |window|),
+ * cells[1] in mixed rounds (a pair's two known strands as one task: half of that). Synchronises the context's streams. */
+int svp_k1_cells(svp_ctx *ctx, double *cells /* 2 entries */, int reset);
+
 /* Measures the sustained rate of the DPX-class packed 16x2 instructions the score kernel is made of
  * (VIADDMNMX / VIMNMX3 / IADD), in lane-operations per second over the whole chip. */
 int svp_probe_dpx(svp_ctx *ctx, double *viaddmax_lane_ops, double *vimax3_lane_ops, double *mix_lane_ops);
 
 /* Per-kernel launch counts and CUDA-event milliseconds accumulated since the last reset.
- * names: k1_score, k1_trace, k2_traceback, k3_pileup_vote, k5_final, k5_traceback, pack */
-int svp_stats(svp_ctx *ctx, int32_t *n_launches, double *ms_by_kernel /* 8 entries */, int reset);
+ * names: k1_score (regular rounds), k1_trace, k2_traceback, k3_pileup_vote, k5_final, k5_traceback, pack, other,
+ * k1_score_mixed (score pass of the mixed rounds: list building + mixed + regular launches) */
+int svp_stats(svp_ctx *ctx, int32_t *n_launches, double *ms_by_kernel /* 9 entries */, int reset);
 
 /* A polish batch of >= 8 variants is split into n_lanes contiguous parts that run concurrently on the same GPU
  * (own stream, arenas and host thread per lane), so that the latency-bound stages of one part overlap the

@@ -70,7 +70,7 @@ EXPORTS = ["svp_create", "svp_destroy", "svp_last_error", "svp_version", "svp_al
            "svp_polish_batch", "svp_polish_rerun", "svp_final_align_batch", "svp_assign_quality", "svp_submit_polish", "svp_wait_any",
            "svp_debug_round", "svp_probe_dpx", "svp_stats", "svp_set_lanes", "svp_refine_variant", "svp_refine_info",
            "svp_format_quality", "svp_record_supports_variant", "svp_read_region_boundaries",
-           "svp_alignment_length_in_ref", "svp_cut_down_high_coverage", "svp_merge_record_group"]
+           "svp_alignment_length_in_ref", "svp_cut_down_high_coverage", "svp_merge_record_group", "svp_k1_cells"]
 
 _lib = None
 
@@ -113,6 +113,7 @@ def lib():
         L.svp_read_region_boundaries.argtypes = [C.c_int32, C.c_char_p, u32p, C.c_int32, C.c_int32, C.c_int32, i32p, i32p]
         L.svp_alignment_length_in_ref.argtypes = [C.c_char_p, u32p, C.c_int32]
         L.svp_cut_down_high_coverage.argtypes = [C.c_int32, i32p, u8p, i32p, C.c_int32, i32p]
+        L.svp_k1_cells.argtypes = [C.c_void_p, f64p, C.c_int]
         L.svp_merge_record_group.argtypes = [C.c_int32, C.POINTER(BamRecord), i32p, i32p, C.c_char_p, u32p, C.c_int32, i32p,
                                              C.c_char_p, C.c_int32, i32p]
         _lib = L
@@ -255,7 +256,8 @@ def merge_alignments(records):
     return out
 
 
-STAT_NAMES = ["k1_score", "k1_trace", "k2_traceback", "k3_pileup_vote", "k5_final", "k5_traceback", "pack", "other"]
+STAT_NAMES = ["k1_score", "k1_trace", "k2_traceback", "k3_pileup_vote", "k5_final", "k5_traceback", "pack", "other",
+              "k1_score_mixed"]
 
 
 class Context:
@@ -415,11 +417,18 @@ class Context:
         self._check(self.L.svp_probe_dpx(self.h, C.byref(a), C.byref(b), C.byref(c)), "svp_probe_dpx")
         return dict(viaddmax=a.value, vimax3=b.value, mix=c.value)
 
+    def k1_cells(self, reset=0, split=False):
+        """DP cells computed by the score kernel for polish batches since the last reset (svp_k1_cells);
+        split: (regular rounds, mixed rounds)"""
+        v = (C.c_double * 2)()
+        self._check(self.L.svp_k1_cells(self.h, v, reset), "svp_k1_cells")
+        return v[0] + v[1] if not split else (v[0], v[1])
+
     def set_lanes(self, n):
         """number of concurrent parts a polish batch is split into on this GPU (svp_set_lanes)"""
         self._check(self.L.svp_set_lanes(self.h, int(n)), "svp_set_lanes")
 
     def stats(self, reset=0):
-        n = C.c_int32(); ms = (C.c_double * 8)()
+        n = C.c_int32(); ms = (C.c_double * 9)()
         self.L.svp_stats(self.h, C.byref(n), ms, reset)
         return n.value, dict(zip(STAT_NAMES, list(ms)))

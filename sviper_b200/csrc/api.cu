@@ -43,10 +43,14 @@ static int init_kernel_attrs(int device)
         return cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, want < 0 ? room : std::min(want, room)) ==
                cudaSuccess;
     };
-    bool ok = set_max((const void *)svp::k1_score_kernel<svp::K1_G, 19>, svp::K1Shape<svp::K1_G, 19>::SMEM_BYTES) &&
-              set_max((const void *)svp::k1_score_kernel<svp::K1_G, 32>, svp::K1Shape<svp::K1_G, 32>::SMEM_BYTES) &&
-              set_max((const void *)svp::k1_score_kernel<svp::K1_GW, 5>, svp::K1Shape<svp::K1_GW, 5>::SMEM_BYTES) &&
-              set_max((const void *)svp::k1_score_kernel<svp::K1_GW, 8>, svp::K1Shape<svp::K1_GW, 8>::SMEM_BYTES) &&
+    bool ok = set_max((const void *)svp::k1_score_kernel<svp::K1_G, 19, false>, svp::K1Shape<svp::K1_G, 19>::SMEM_BYTES) &&
+              set_max((const void *)svp::k1_score_kernel<svp::K1_G, 32, false>, svp::K1Shape<svp::K1_G, 32>::SMEM_BYTES) &&
+              set_max((const void *)svp::k1_score_kernel<svp::K1_GW, 5, false>, svp::K1Shape<svp::K1_GW, 5>::SMEM_BYTES) &&
+              set_max((const void *)svp::k1_score_kernel<svp::K1_GW, 8, false>, svp::K1Shape<svp::K1_GW, 8>::SMEM_BYTES) &&
+              set_max((const void *)svp::k1_score_kernel<svp::K1_G, 19, true>, svp::K1Shape<svp::K1_G, 19>::SMEM_BYTES) &&
+              set_max((const void *)svp::k1_score_kernel<svp::K1_G, 32, true>, svp::K1Shape<svp::K1_G, 32>::SMEM_BYTES) &&
+              set_max((const void *)svp::k1_score_kernel<svp::K1_GW, 5, true>, svp::K1Shape<svp::K1_GW, 5>::SMEM_BYTES) &&
+              set_max((const void *)svp::k1_score_kernel<svp::K1_GW, 8, true>, svp::K1Shape<svp::K1_GW, 8>::SMEM_BYTES) &&
               set_max((const void *)svp::k3_pileup_vote_kernel, -1) &&
               set_max((const void *)svp::k5_final_kernel<true>, -1);
     if (!ok) return SVP_ERR_CUDA;
@@ -101,6 +105,8 @@ static svp_ctx *make_ctx(int cuda_device, void *cuda_stream, bool is_lane)
     if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) ctx->arena_budget = (size_t)(free_b * 0.6);
     const char *fw = getenv("SVP_FULL_WINDOW");
     if (fw && fw[0] == '1') ctx->full_window = 1;
+    const char *nm = getenv("SVP_NO_MIXED");
+    if (nm && atoi(nm) == 1) ctx->mixed_rounds = false;
     const char *ln = getenv("SVP_LANES");
     if (ln && atoi(ln) >= 1) ctx->n_lanes = std::min(atoi(ln), SVP_MAX_LANES);
     if (is_lane) ctx->n_lanes = 1;
@@ -285,6 +291,24 @@ int svp_stats(svp_ctx *ctx, int32_t *n_launches, double *ms_by_kernel, int reset
         if (reset == 1) { c->n_launches = 0; for (int i = 0; i < ST_N; ++i) c->ms[i] = 0; }
         if (reset == 2) c->timing = true;    // enable per-kernel CUDA-event timing (events resolved lazily, no extra syncs)
         if (reset == 3) c->timing = false;
+    }
+    return SVP_OK;
+}
+
+int svp_k1_cells(svp_ctx *ctx, double *cells, int reset)
+{
+    if (!ctx || !cells) return SVP_ERR_ARG;
+    std::vector<svp_ctx *> all(1, ctx);
+    all.insert(all.end(), ctx->lanes.begin(), ctx->lanes.end());
+    cells[0] = cells[1] = 0;
+    for (svp_ctx *c : all)
+    {
+        if (!c->mixcnt.p || !c->mixcnt_zeroed) continue;
+        unsigned long long v[2] = {0, 0};
+        CK(cudaStreamSynchronize(c->stream));
+        CK(cudaMemcpy(v, c->mixcnt.as<char>() + 32, 16, cudaMemcpyDeviceToHost));
+        cells[0] += (double)v[0]; cells[1] += (double)v[1];
+        if (reset) CK(cudaMemset(c->mixcnt.as<char>() + 32, 0, 16));
     }
     return SVP_OK;
 }

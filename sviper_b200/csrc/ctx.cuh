@@ -75,7 +75,7 @@ struct HostStage
     }
 };
 
-enum { ST_K1 = 0, ST_K1T, ST_K2, ST_K3, ST_K5, ST_K5TB, ST_PACK, ST_OTHER, ST_N };
+enum { ST_K1 = 0, ST_K1T, ST_K2, ST_K3, ST_K5, ST_K5TB, ST_PACK, ST_OTHER, ST_K1M /* score pass of mixed rounds */, ST_N };
 
 // device-resident packed sequences (reads or windows)
 struct DevSeqs
@@ -135,6 +135,11 @@ struct svp_ctx
     int64_t E_total = 0;
     // ---- polish pipeline ----
     DevBuf descs, states, states_init, pair_task, cons0, cons1, inslen, voff, profile, cov, isgap, decision, proper, cons_init;
+    // strand certificates (k1_score.cuh, K1Mix): per-task strand state, per-round task lists, per-window edit density
+    DevBuf sstate, reg19, reg32, mix19, mix32, mixcnt, edit, emax;
+    bool mixcnt_zeroed = false;             // mixcnt: 4 list counters (reset every round) + the DP cell counter at byte 32
+    int64_t pairs_total = 0;
+    bool mixed_rounds = true;               // SVP_NO_MIXED=1 turns the mixed tasks off (A/B measurements)
     struct PolishLayout *resident = nullptr;   // last svp_polish_batch, kept for svp_polish_rerun
     int resident_nv = 0;
     // ---- final alignment ----

@@ -49,7 +49,34 @@ struct K1Shape
     static_assert(PST % 32 == 0 && TASK_WORDS % 4 == 0, "profile rows must keep bank phase and 16-byte alignment");
 };
 
-template <int G, int RPL>
+// Rounds >= 2 of a polish batch (MIXED): the strand of a read is known from an earlier round, together with an upper bound
+// on the score of its OTHER strand, so the two halves of the s16x2 lanes carry the known strands of the two mates of a
+// pair instead of the two strands of one read (half the tasks). Exactness: a consensus edit changes the score of an
+// alignment that crosses it by at most 7 (substitution: 1 - (-4) = 5; deleted column: the path takes it as a new
+// 1-column gap, 6; inserted column aligned to a read base: that base becomes a 1-base gap instead of a match, 7), so for
+// every alignment P' of the other strand to the NEW consensus that spans at most W columns there is one to the OLD
+// consensus with score >= score(P') - E, E = the largest sum of these costs over any W consecutive columns (k3 computes it
+// per window for W = 320 and 512). An alignment with score >= S >= 0 has at most R - S - 5 <= R deleted columns, i.e.
+// spans at most 2R <= W columns. Hence with bound' = max(bound + E, -6) (a path longer than W scores < -5):
+// S >= 0 and S > bound' proves that no alignment of the other strand reaches S -- mapping.h:121 picks the same strand --
+// and bound' is the other strand's bound for the next round. Reads that fail the test are appended to the regular
+// (both strands) list of the same round.
+struct K1Mix
+{
+    const int32_t *n_dev;      // number of tasks (pairs if MIXED) of this launch, on the device; null: `ntasks`
+    int32_t *sstate;           // per task: bit 0 strand known, bit 1 is_rc, bits 16..31 bound on the other strand's score
+    const int32_t *emax;       // per window: edit cost E for W = 320, W = 512
+    int32_t *fb19, *fb32;      // regular lists the failures are appended to
+    int32_t *fb_cnt;           // their counters [2]
+    unsigned long long *cells; // DP cells computed (statistics)
+};
+
+__device__ __forceinline__ uint32_t k1_pk2(int a, int b)
+{
+    return (uint32_t)((K1_BIAS + a) & 0xffff) | ((uint32_t)((K1_BIAS + b) & 0xffff) << 16);
+}
+
+template <int G, int RPL, bool MIXED>
 __global__ void __launch_bounds__(K1_THREADS, 4) k1_score_kernel(const int32_t *__restrict__ task_read,
                                                        const int32_t *__restrict__ task_win,
                                                        const int32_t *__restrict__ task_idx, int ntasks,
@@ -58,7 +85,7 @@ __global__ void __launch_bounds__(K1_THREADS, 4) k1_score_kernel(const int32_t *
                                                        const uint8_t *__restrict__ win_bytes,
                                                        const int64_t *__restrict__ win_byte_off,
                                                        ScoreOut *__restrict__ out,
-                                                       uint32_t one /* always 1; opaque to the compiler */)
+                                                       uint32_t one /* always 1; opaque to the compiler */, K1Mix mix)
 {
     using Sh = K1Shape<G, RPL>;
     constexpr int NSLOT = Sh::NSLOT, PST = Sh::PST, KPAD = Sh::KPAD, NQ = (RPL + 3) / 4;
@@ -67,21 +94,36 @@ __global__ void __launch_bounds__(K1_THREADS, 4) k1_score_kernel(const int32_t *
     const int slot = blockIdx.x * Sh::TASKS_PER_BLOCK + grp;
     uint32_t *prof = k1_smem + grp * Sh::TASK_WORDS;   // prof[c][g][k]
 
+    if (mix.n_dev)
+    {
+        ntasks = *mix.n_dev;                                          // the grid was sized for an upper bound
+        if (blockIdx.x * Sh::TASKS_PER_BLOCK >= ntasks) return;       // (whole block: no shuffle partner is left behind)
+    }
     int R = 0, L = 0, runit = 0, task = -1;
+    int R2 = 0, runit2 = 0, task2 = -1, rcA = 0, rcB = 0, wid = 0;   // MIXED: second read of the pair, known strands
     const uint8_t *wb = win_bytes;   // the window as bytes 0..4 (zero padded behind its end)
     if (slot < ntasks)
     {
-        task = task_idx ? task_idx[slot] : slot;
-        int rid = task_read[task], wid = task_win[task];
+        if (MIXED) { task = task_idx[2 * slot]; task2 = task_idx[2 * slot + 1]; }
+        else task = task_idx ? task_idx[slot] : slot;
+        int rid = task_read[task];
+        wid = task_win[task];
         if (win_done && win_done[wid]) task = -1;       // window already converged: nothing to do
         else
         {
             R = reads.len[rid]; runit = reads.off32[rid];
             L = wins.len[wid]; wb = win_bytes + win_byte_off[wid];
+            if (MIXED)
+            {
+                const int rid2 = task_read[task2];
+                R2 = reads.len[rid2]; runit2 = reads.off32[rid2];
+                rcA = (mix.sstate[task] >> 1) & 1; rcB = (mix.sstate[task2] >> 1) & 1;
+            }
         }
     }
     const bool live = task >= 0;
     const int pad = NSLOT - R;   // extra "row 0"s at the top
+    const int pad2 = NSLOT - R2;
 
     constexpr uint32_t GE2 = 0xFFFFFFFFu;           // (-1,-1)
     constexpr uint32_t GO2 = 0u - 0x00060006u;      // 32-bit add of this subtracts 6 from both halves (no borrow)
@@ -94,29 +136,50 @@ __global__ void __launch_bounds__(K1_THREADS, 4) k1_score_kernel(const int32_t *
     for (int k = 0; k < RPL; ++k)
     {
         int row = g * RPL + k - pad + 1;   // 1-based read row; <= 0 -> pad
+        int row2 = MIXED ? g * RPL + k - pad2 + 1 : row;   // MIXED: the high half is another read
         int rf = -1, rr = -1;
-        if (row >= 1)
+        if (!MIXED)
         {
-            rf = seq_base(reads, runit, row - 1);
-            int b = seq_base(reads, runit, R - row);
-            rr = (b < 4) ? 3 - b : 4;
+            if (row >= 1)
+            {
+                rf = seq_base(reads, runit, row - 1);
+                int b = seq_base(reads, runit, R - row);
+                rr = (b < 4) ? 3 - b : 4;
+            }
+        }
+        else
+        {
+            // low half: read A on its known strand, high half: read B on its known strand
+            if (row >= 1)
+            {
+                int b = seq_base(reads, runit, rcA ? R - row : row - 1);
+                rf = rcA ? ((b < 4) ? 3 - b : 4) : b;
+            }
+            if (row2 >= 1)
+            {
+                int b = seq_base(reads, runit2, rcB ? R2 - row2 : row2 - 1);
+                rr = rcB ? ((b < 4) ? 3 - b : 4) : b;
+            }
         }
 #pragma unroll
         for (int c = 0; c < 5; ++c)
         {
             uint32_t sf = (row < 1) ? 6u : ((c == rf) ? 7u : 2u);   // sub - go
-            uint32_t sr = (row < 1) ? 6u : ((c == rr) ? 7u : 2u);
+            uint32_t sr = (row2 < 1) ? 6u : ((c == rr) ? 7u : 2u);
             prof[c * PST + g * KPAD + k] = sf | (sr << 16);
         }
         int s0 = (row >= 1) ? -(5 + row) : 0;
-        so[k] = k1_pk(s0 + GAP_OPEN);
+        int s02 = (row2 >= 1) ? -(5 + row2) : 0;
+        so[k] = MIXED ? k1_pk2(s0 + GAP_OPEN, s02 + GAP_OPEN) : k1_pk(s0 + GAP_OPEN);
         h[k] = NEG2;
     }
     uint32_t prev_up;   // S[i-1][j-1] + go for this lane's first row
     {
         int rowa = g * RPL - pad;   // row above the first slot
         int sa = (rowa >= 1) ? -(5 + rowa) : 0;
-        prev_up = (g == 0) ? ROW0_SO : k1_pk(sa + GAP_OPEN);
+        int rowa2 = g * RPL - pad2;
+        int sa2 = (rowa2 >= 1) ? -(5 + rowa2) : 0;
+        prev_up = (g == 0) ? ROW0_SO : (MIXED ? k1_pk2(sa + GAP_OPEN, sa2 + GAP_OPEN) : k1_pk(sa + GAP_OPEN));
     }
     uint32_t out_so0 = so[RPL - 1], out_v0 = NEG2, out_so1 = so[RPL - 1], out_v1 = NEG2;
     uint32_t best = so[RPL - 1];
@@ -200,11 +263,75 @@ __global__ void __launch_bounds__(K1_THREADS, 4) k1_score_kernel(const int32_t *
     }
     if (g == G - 1 && live)
     {
-        ScoreOut o;
-        o.score_f = (int)(best & 0xffff) - K1_BIAS - GAP_OPEN;
-        o.score_r = (int)(best >> 16) - K1_BIAS - GAP_OPEN;
-        o.col_f = colF; o.col_r = colR;
-        out[task] = o;
+        const int s_lo = (int)(best & 0xffff) - K1_BIAS - GAP_OPEN, s_hi = (int)(best >> 16) - K1_BIAS - GAP_OPEN;
+        if (!MIXED)
+        {
+            ScoreOut o;
+            o.score_f = s_lo; o.score_r = s_hi;
+            o.col_f = colF; o.col_r = colR;
+            out[task] = o;
+            if (mix.sstate)
+            {
+                const int rc = !(s_lo > s_hi);                       // mapping.h:121
+                int lose = rc ? s_lo : s_hi;
+                lose = max(-32768, min(32767, lose));
+                mix.sstate[task] = (int32_t)(((uint32_t)lose << 16) | (uint32_t)(rc << 1) | 1u);
+            }
+            if (mix.cells) atomicAdd(mix.cells, 2ull * (unsigned long long)R * (unsigned long long)L);
+        }
+        else
+        {
+#pragma unroll
+            for (int hh = 0; hh < 2; ++hh)
+            {
+                const int t = hh ? task2 : task, sc = hh ? s_hi : s_lo, col = hh ? colR : colF, rc = hh ? rcB : rcA;
+                const int Rt = hh ? R2 : R;
+                const int old = mix.sstate[t] >> 16;
+                const int nb = max(old + mix.emax[2 * wid + (Rt > 152)], -6);
+                if (sc >= 0 && sc > nb && nb < 32000)
+                {
+                    ScoreOut o;
+                    o.score_f = rc ? nb : sc; o.score_r = rc ? sc : nb;   // the loser's entry is only ever compared
+                    o.col_f = rc ? 0 : col; o.col_r = rc ? col : 0;
+                    out[t] = o;
+                    mix.sstate[t] = (int32_t)(((uint32_t)nb << 16) | (uint32_t)(rc << 1) | 1u);
+                }
+                else
+                {
+                    mix.sstate[t] = 0;
+                    const int cls = Rt > 152;
+                    const int at = atomicAdd(mix.fb_cnt + cls, 1);
+                    (cls ? mix.fb32 : mix.fb19)[at] = t;
+                }
+            }
+            if (mix.cells) atomicAdd(mix.cells, (unsigned long long)(R + R2) * (unsigned long long)L);
+        }
     }
+}
+
+// Rounds >= 2: splits the live pairs of a polish batch into mixed tasks (both strands known: one task per pair) and
+// regular tasks (both strands of one read). cnt: [0] regular <= 152 rows, [1] regular <= 256, [2] mixed <= 152, [3] mixed <= 256
+__global__ void mix_plan_kernel(const int32_t *__restrict__ pair_task, int64_t npairs, const int32_t *__restrict__ task_read,
+                                const int32_t *__restrict__ task_win, const int32_t *__restrict__ read_len,
+                                const uint8_t *__restrict__ win_done, const int32_t *__restrict__ sstate,
+                                int32_t *__restrict__ reg19, int32_t *__restrict__ reg32, int32_t *__restrict__ mix19,
+                                int32_t *__restrict__ mix32, int32_t *__restrict__ cnt)
+{
+    const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= npairs) return;
+    const int t1 = pair_task[2 * p], t2 = pair_task[2 * p + 1];
+    if (t1 < 0) return;
+    if (win_done[task_win[t1]]) return;
+    const int R1 = read_len[task_read[t1]], R2 = t2 >= 0 ? read_len[task_read[t2]] : 0;
+    if (t2 >= 0 && (sstate[t1] & 1) && (sstate[t2] & 1))
+    {
+        const int cls = (R1 > 152 || R2 > 152);
+        const int at = atomicAdd(cnt + 2 + cls, 1);
+        int32_t *m = cls ? mix32 : mix19;
+        m[2 * at] = t1; m[2 * at + 1] = t2;
+        return;
+    }
+    { const int cls = R1 > 152; (cls ? reg32 : reg19)[atomicAdd(cnt + cls, 1)] = t1; }
+    if (t2 >= 0) { const int cls = R2 > 152; (cls ? reg32 : reg19)[atomicAdd(cnt + cls, 1)] = t2; }
 }
 }  // namespace svp

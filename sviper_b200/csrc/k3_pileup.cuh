@@ -67,7 +67,12 @@ struct K3Buffers
     uint8_t *isgap;
     uint8_t *decision;      // per view column: 0..4 emit that base, 255 emit nothing
     uint8_t *proper;        // per pair
+    uint8_t *edit;          // per view column: by how much this column can change the score of an alignment that crosses it
+                            // (0 unchanged, 5 substituted, 6 deleted consensus column, 7 emitted inserted column)
+    int32_t *emax;          // per variant: largest sum of these costs over any 320 / 512 consecutive columns of the new
+                            // consensus (upper bound; feeds the strand certificate of k1_score.cuh, K1Mix)
 };
+constexpr int K3_HB = 1024; // histogram bins of the edit cost, 32 new-consensus columns each (the last bin takes the rest)
 
 __device__ __forceinline__ int oriented_base(const SeqStore &reads, int rid, int R, int is_rc, int q)
 {
@@ -95,6 +100,9 @@ __global__ void __launch_bounds__(K3_THREADS) k3_pileup_vote_kernel(
     uint32_t *cov = buf.cov + d.prof_off;
     uint8_t *isgap = buf.isgap + d.prof_off;
     uint8_t *decision = buf.decision + d.prof_off;
+    uint8_t *edit = buf.edit + d.prof_off;
+    __shared__ int sh_hist[K3_HB + 32];
+    __shared__ int sh_emax[2];
     uint8_t *proper = buf.proper + d.pair_base / 2;
     const int32_t *pt = pair_task + d.pair_base;
 
@@ -330,6 +338,7 @@ __global__ void __launch_bounds__(K3_THREADS) k3_pileup_vote_kernel(
                 for (int s = 0; s < 6; ++s) profile[(size_t)col * 6 + s] = c[s];
                 cov[col] = ck; isgap[col] = 1;
                 decision[col] = ins_in ? (uint8_t)vote(c, ck, 1, -1) : 255;
+                edit[col] = decision[col] != 255 ? 7 : 0;
             }
             {
                 int col = col0 + il;
@@ -338,6 +347,7 @@ __global__ void __launch_bounds__(K3_THREADS) k3_pileup_vote_kernel(
                 cov[col] = cv; isgap[col] = 0;
                 int bs = cons[p];
                 decision[col] = (p >= flank && p < L - flank) ? (uint8_t)vote(m, cv, 0, bs) : 255;
+                edit[col] = ((p >= flank && p < L - flank) && decision[col] != bs) ? (decision[col] == 255 ? 6 : 5) : 0;
             }
         }
         __syncwarp();
@@ -361,8 +371,12 @@ __global__ void __launch_bounds__(K3_THREADS) k3_pileup_vote_kernel(
                     double c[6];
 #pragma unroll
                     for (int q = 0; q < 6; ++q) c[q] = profile[(size_t)col * 6 + q];
-                    if (k < il) decision[col] = ins_in ? (uint8_t)vote(c, cov[col], 1, -1) : 255;
-                    else decision[col] = (p >= flank && p < L - flank) ? (uint8_t)vote(c, cov[col], 0, cons[p]) : 255;
+                    if (k < il) { decision[col] = ins_in ? (uint8_t)vote(c, cov[col], 1, -1) : 255; edit[col] = decision[col] != 255 ? 7 : 0; }
+                    else
+                    {
+                        decision[col] = (p >= flank && p < L - flank) ? (uint8_t)vote(c, cov[col], 0, cons[p]) : 255;
+                        edit[col] = ((p >= flank && p < L - flank) && decision[col] != cons[p]) ? (decision[col] == 255 ? 6 : 5) : 0;
+                    }
                 }
             }
         }
@@ -378,6 +392,9 @@ __global__ void __launch_bounds__(K3_THREADS) k3_pileup_vote_kernel(
         const int ve = voff[L - flank] + inslen[L - flank];         // column of base L - flank
         int carry = flank;
         for (int i = tid; i < flank; i += K3_THREADS) next[i] = cons[i];
+        for (int i = tid; i < K3_HB + 32; i += K3_THREADS) sh_hist[i] = 0;
+        if (tid < 2) sh_emax[tid] = 0;
+        __syncthreads();
         for (int base = vb; base < ve; base += K3_THREADS)
         {
             int col = base + tid;
@@ -385,8 +402,27 @@ __global__ void __launch_bounds__(K3_THREADS) k3_pileup_vote_kernel(
             int x = (dcs != 255), ex, tot;
             BS(tmp.s).ExclusiveSum(x, ex, tot);
             if (x && carry + ex < d.Lcap) next[carry + ex] = (uint8_t)dcs;
+            // edit cost in NEW-consensus coordinates: an emitted column sits at carry + ex, a deleted one is booked on
+            // the column that follows it
+            if (col < ve && edit[col]) atomicAdd(&sh_hist[min((carry + ex) >> 5, K3_HB - 1)], (int)edit[col]);
             carry += tot;
             __syncthreads();
+        }
+        {
+            // W consecutive columns touch at most W / 32 + 1 bins
+            int m0 = 0, m1 = 0;
+            for (int i = tid; i < K3_HB; i += K3_THREADS)
+            {
+                int a0 = 0;
+                for (int j = 0; j < 11; ++j) a0 += sh_hist[i + j];
+                int a1 = a0;
+                for (int j = 11; j < 17; ++j) a1 += sh_hist[i + j];
+                m0 = max(m0, a0); m1 = max(m1, a1);
+            }
+            m0 = __reduce_max_sync(0xffffffffu, m0); m1 = __reduce_max_sync(0xffffffffu, m1);
+            if ((tid & 31) == 0) { atomicMax(&sh_emax[0], m0); atomicMax(&sh_emax[1], m1); }
+            __syncthreads();
+            if (tid < 2) buf.emax[2 * v + tid] = sh_emax[tid];
         }
         const int newL = carry + flank;
         if (newL > d.Lcap) { if (tid == 0) { states[v].err = 5; states[v].done = 1; } return; }

@@ -232,3 +232,36 @@ def test_vcf_fields_end_to_end(ctx):
         wrong = dict(c, sv_length=3 * c["sv_length"] + 50)
         bad = api.evaluate_final_mapping(wrong, g["cigar"], g["polished"], begin, v["k"])
         assert bad["filter"] == "FAIL5" and bad["info"] == c["info"] and bad["ref_pos"] == c["ref_pos"]
+
+
+def test_mixed_strand_rounds_are_exact_and_save_cells(ctx, config1_batch):
+    """Rounds >= 2 run the two known strands of a pair as ONE packed task where the strand certificate holds
+    (k1_score.cuh, K1Mix): same results as with SVP_NO_MIXED-style regular rounds (here: against the oracle-checked
+    results of the other tests through batch equality), and the score kernel computes clearly fewer cells than the
+    reference's 2 x |read| x |window| per read and alignment round."""
+    ctx.k1_cells(reset=1)
+    res = ctx.polish_batch(config1_batch, with_final=True)
+    cells = ctx.k1_cells(reset=1)
+    algorithmic = 0
+    for v, r in zip(config1_batch, res):
+        nreads = sum(1 for x in v["reads1"] if len(x)) + sum(1 for x in v["reads2"] if len(x))
+        algorithmic += 2 * 150 * len(v["consensus"]) * nreads * r["alignment_rounds"]
+    assert 0.5 * algorithmic < cells < 0.9 * algorithmic
+    # every variant again as a batch of its own (other batch composition, other lists): identical results
+    for v, r in list(zip(config1_batch, res))[:6]:
+        one = ctx.polish_batch([v], with_final=True)[0]
+        assert same(one, r)
+    # A/B: a context whose rounds are all regular (both strands of every read, SVP_NO_MIXED=1)
+    import os
+    from sviper_b200 import api
+    os.environ["SVP_NO_MIXED"] = "1"
+    try:
+        plain = api.Context(0)
+    finally:
+        del os.environ["SVP_NO_MIXED"]
+    plain.k1_cells(reset=1)
+    res0 = plain.polish_batch(config1_batch, with_final=True)
+    cells0 = plain.k1_cells(reset=1)
+    plain.close()
+    assert all(same(a, b) for a, b in zip(res, res0))
+    assert abs(cells0 / algorithmic - 1.0) < 0.02
