@@ -157,6 +157,38 @@ def test_polish_small_batch(ctx):
     check_polish(ctx, vs)
 
 
+def test_polish_strand_certificate_corner_cases(ctx):
+    """Inputs aimed at the strand certificate of the mixed rounds (k1_score.cuh, K1Mix): reverse-complement palindromes
+    and near-palindromes (both strands tie or differ by one mismatch: mapping.h:121 must keep choosing the same one),
+    reads unrelated to the window (both strands score alike and low), low-complexity reads, and a consensus so noisy
+    that the windows change a lot between rounds. Everything against the oracle's literal both-strands restatement."""
+    rng = np.random.default_rng(4711)
+    vs = []
+    for s_ in range(8):
+        v = rc.small_variant(900 + s_, L_core=260, flank=40, read_len=60, n_pairs=40, err=[0.05, 0.12, 0.2][s_ % 3])
+        R = 60
+        for i in range(0, len(v["reads1"]), 5):
+            half = rng.integers(0, 4, R // 2).astype(np.uint8)
+            pal = np.concatenate([half, synth.revcomp(half)])                   # read == revcomp(read)
+            if i % 10 == 0:
+                pal[int(rng.integers(0, R))] = (pal[int(rng.integers(0, R))] + 1) % 4   # near-palindrome
+            v["reads1"][i] = pal
+        for i in range(1, len(v["reads2"]), 7):
+            if len(v["reads2"][i]):
+                v["reads2"][i] = rng.integers(0, 4, R).astype(np.uint8)         # unrelated mate
+        for i in range(2, len(v["reads1"]), 9):
+            v["reads1"][i] = np.tile(np.array([0, 3], np.uint8), R // 2)        # ATAT...: its own reverse complement, shifted
+        # palindromic stretch inside the window itself: reads on it align equally well on both strands
+        t = v["consensus"]
+        mid = len(t) // 2
+        half = t[mid - 30:mid].copy()
+        v["consensus"] = np.concatenate([t[:mid], synth.revcomp(half), t[mid + 30:]])
+        v["truth"] = v["consensus"].copy()
+        v["ref_part"] = v["truth"]
+        vs.append(v)
+    check_polish(ctx, vs)
+
+
 def test_polish_golden_fixture(ctx):
     cases = rc.read_cases(os.path.join(os.path.dirname(__file__), "golden", "cases.txt"))
     with open(os.path.join(os.path.dirname(__file__), "golden", "expected.txt")) as f:
