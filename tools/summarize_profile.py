@@ -17,7 +17,8 @@ import sys
 BENCH_KEY = {"k1_score_kernel": "k1_score", "k1_band_kernel": "k1_trace", "k1_trace_kernel": "k1_trace",
              "k2_traceback_kernel": "k2_traceback", "k3_pileup_vote_kernel": "k3_pileup_vote",
              "k5_final_kernel": "k5_final", "k5_traceback_kernel": "k5_traceback", "pack_kernel": "pack",
-             "window_refresh_kernel": "pack"}
+             "window_refresh_kernel": "pack", "k1_score_kernel (mixed rounds)": "k1_score_mixed",
+             "mix_plan_kernel": "k1_score_mixed"}
 RAW_KEEP = ["gpu__time_duration.sum", "launch__grid_size", "launch__block_size", "launch__registers_per_thread",
             "launch__occupancy_limit_shared_mem", "launch__occupancy_limit_registers",
             "sm__warps_active.avg.per_cycle_active", "smsp__issue_active.avg.per_cycle_active",
@@ -79,8 +80,14 @@ def main():
     seq = read_launches(os.path.join(src, tag + "_launches.csv"))
     step = last_step(seq)
     agg = collections.OrderedDict()
+    mixed_round = False          # the score-pass launches behind the step's first mix_plan_kernel belong to mixed rounds
     for k, v, _ in step:
-        a = agg.setdefault(short(k), [0, 0.0])
+        name = short(k)
+        if name == "mix_plan_kernel":
+            mixed_round = True
+        if name == "k1_score_kernel" and mixed_round:
+            name = "k1_score_kernel (mixed rounds)"
+        a = agg.setdefault(name, [0, 0.0])
         a[0] += 1
         a[1] += v
     tot = sum(a[1] for a in agg.values())
@@ -114,8 +121,20 @@ def main():
     L.append("Bench line (`%s_bench.json`): value %.0f %s, %.3f ms/step, e2e %.0f, roofline.frac %.3f (%s), gpu_launches %d.\n"
              % (tag, bench["value"], bench["unit"], bench["ms_per_step"], bench["e2e"]["value"], bench["roofline"]["frac"],
                 bench["roofline"]["kernel"], bench["gpu_launches"]))
-    for f in sorted(os.listdir(src)):
-        if f.startswith(tag + "_") and f.endswith(".ncu-rep"):
+    reps = [f for f in sorted(os.listdir(src)) if f.startswith(tag + "_") and f.endswith(".ncu-rep")]
+    if not reps:
+        # no new full captures: keep the sections of the existing summary (their raw pages are already under dst)
+        old = os.path.join(dst, tag + "_summary.md")
+        if os.path.exists(old):
+            txt = open(old).read()
+            at = txt.find("## `")
+            if at >= 0:
+                L.append("(full captures below: taken before the mixed rounds were added; the regular kernel's inner loop and "
+                         "register count are unchanged)\n")
+                L.append(txt[at:].rstrip("\n"))
+                L.append("")
+    for f in reps:
+        if True:
             met, raw = raw_page(os.path.join(src, f))
             name = f[:-len(".ncu-rep")]
             open(os.path.join(dst, name + "_ncu_raw.csv"), "w").write(raw)
