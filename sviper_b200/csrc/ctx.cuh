@@ -138,7 +138,7 @@ struct svp_ctx
     // strand certificates (k1_score.cuh, K1Mix): per-task strand state, per-round task lists, per-window edit density
     DevBuf sstate, reg19, reg32, mix19, mix32, mixcnt, edit, emax;
     bool mixcnt_zeroed = false;             // mixcnt: 4 list counters (reset every round) + the DP cell counter at byte 32
-    int64_t pairs_total = 0;
+    int64_t pairs_total = 0, n_mateless = 0;   // pairs of the batch; pairs with a dummy mate
     bool mixed_rounds = true;               // SVP_NO_MIXED=1 turns the mixed tasks off (A/B measurements)
     struct PolishLayout *resident = nullptr;   // last svp_polish_batch, kept for svp_polish_rerun
     int resident_nv = 0;

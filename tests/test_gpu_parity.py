@@ -189,6 +189,20 @@ def test_polish_strand_certificate_corner_cases(ctx):
     check_polish(ctx, vs)
 
 
+def test_polish_mateless_reads(ctx):
+    """batches of mate-less reads (dummy mates, basics.h:317,398): no pair can be mixed, every round stays regular -- a few
+    of them (wide shape in rounds >= 2) and more than 3,000 (throughput shape)"""
+    def strip_mates(v):
+        v["reads2"] = [np.zeros(0, np.uint8) for _ in v["reads2"]]
+        v["quals2"] = [np.zeros(0, np.uint8) for _ in v["quals2"]]
+        v["ref_part"] = v["truth"]
+        return v
+    check_polish(ctx, [strip_mates(rc.small_variant(1200 + s_, n_pairs=30, err=0.08)) for s_ in range(3)])
+    many = [strip_mates(rc.small_variant(1300 + s_, n_pairs=150, err=0.08)) for s_ in range(22)]
+    assert sum(len(v["reads1"]) for v in many) > 3000
+    check_polish(ctx, many)
+
+
 def test_polish_golden_fixture(ctx):
     cases = rc.read_cases(os.path.join(os.path.dirname(__file__), "golden", "cases.txt"))
     with open(os.path.join(os.path.dirname(__file__), "golden", "expected.txt")) as f:
