@@ -29,7 +29,8 @@ extern "C" {
 #define SVP_OK 0
 #define SVP_ERR_CUDA (-1)        /* a CUDA call or kernel failed; svp_last_error() has the text */
 #define SVP_ERR_ARG (-2)         /* invalid argument (empty read1, window shorter than 2*flank, ...) */
-#define SVP_ERR_CAPACITY (-3)    /* a window outgrew its buffers (consensus grew beyond 2x + 4096) */
+#define SVP_ERR_CAPACITY (-3)    /* a window outgrew its buffers (polished sequence longer than svp_window_capacity(len)),
+                                    a caller buffer is too small, or too many read pairs in one variant (~4,000) */
 #define SVP_ERR_UNSUPPORTED (-4) /* read longer than SVP_MAX_READ_LEN */
 
 #define SVP_MAX_READ_LEN 256
@@ -135,7 +136,16 @@ typedef struct
     uint32_t reserved_;
 } svp_result;
 
+/* Per-variant limits (read longer than SVP_MAX_READ_LEN, empty read1, window shorter than 2 x flank, more read pairs than
+ * the pileup kernel stages) are reported in that variant's svp_result.status; such a variant is left out of the device
+ * batch and the OTHER variants of the call are polished normally. The return value is non-zero only when the call as a
+ * whole failed (CUDA error, out of device memory). */
 int svp_polish_batch(svp_ctx *ctx, int32_t n_variants, const svp_window_in *in, svp_result *out);
+
+/* Longest polished sequence a window of consensus_len bases can grow to on the device (consensus_len + consensus_len / 4 +
+ * 512): size svp_result.polished with it; 3 x that + 1024 entries always hold the coverage profile. The reference has no
+ * limit (polishing.h:236-293 appends to a string); a window that outgrows it ends with status SVP_ERR_CAPACITY. */
+int32_t svp_window_capacity(int32_t consensus_len);
 
 /* Re-runs the last svp_polish_batch (every round and the final alignment) from its HBM-resident inputs;
  * nothing is copied from or to the host. Used by bench.py for the device-resident throughput. */
@@ -244,12 +254,22 @@ int svp_merge_record_group(int32_t n, const svp_bam_record *recs, int32_t *chose
                            int32_t *seq_len);
 
 /* ------------------------------------------------------------------------------------------------
- * Batch scheduler facade (replaces the loop body at src/sviper.cpp:43-47): submissions are queued and
- * executed as one device batch on the first svp_wait_any after them. The structs (and everything they
- * point to) must stay valid until their result has been returned.
+ * Asynchronous device batch scheduler (replaces the loop body at src/sviper.cpp:43-47; SURVEY 8b "submissions
+ * asynchronous with an explicit wait"). svp_submit_polish queues one variant and returns at once; one worker thread per
+ * lane (svp_set_lanes) forms device batches from what is queued, runs them (staging, H2D, every round, final alignment,
+ * D2H into the caller's buffers) and hands the results to svp_wait_any in completion order. The lanes run out of phase,
+ * so the copies of one batch overlap the kernels of the others. Thread-safe: any thread may submit, any thread may wait.
+ * Lifetime: *w is copied, but everything it points to, *r and everything *r points to must stay valid until svp_wait_any
+ * has returned that result. A variant outside the per-variant limits completes at once with its status set.
+ * A lane starts a batch when batch_target variants are queued (default 256, env SVP_BATCH_TARGET), on svp_flush, or when
+ * a thread blocks in svp_wait_any with nothing running. Do not call the synchronous batch functions on the same context
+ * while submissions are outstanding.
  * ---------------------------------------------------------------------------------------------- */
 int svp_submit_polish(svp_ctx *ctx, uint64_t tag, const svp_window_in *w, svp_result *r);
-int svp_wait_any(svp_ctx *ctx, uint64_t *tag, svp_result **r);   /* returns 1 when nothing is pending */
+int svp_flush(svp_ctx *ctx);                                     /* start on whatever is queued now */
+int svp_wait_any(svp_ctx *ctx, uint64_t *tag, svp_result **r);   /* blocks; returns 1 when nothing is outstanding */
+int svp_engine_config(svp_ctx *ctx, int32_t batch_target, int32_t max_batch);   /* <= 0: keep */
+int svp_engine_stats(svp_ctx *ctx, uint64_t *batches, uint64_t *variants);      /* device batches formed so far */
 
 /* ------------------------------------------------------------------------------------------------
  * Debug / measurement hooks
@@ -268,6 +288,10 @@ int svp_k1_cells(svp_ctx *ctx, double *cells /* 2 entries */, int reset);
 /* Measures the sustained rate of the DPX-class packed 16x2 instructions the score kernel is made of
  * (VIADDMNMX / VIMNMX3 / IADD), in lane-operations per second over the whole chip. */
 int svp_probe_dpx(svp_ctx *ctx, double *viaddmax_lane_ops, double *vimax3_lane_ops, double *mix_lane_ops);
+
+/* Measures the sustained fp64 add rate of the chip (independent DADD chains, all SMs), in lane-operations per second:
+ * the yardstick of the final-alignment kernel, whose recurrence is 4 DADD + 4 fp64 compares per cell. */
+int svp_probe_fp64(svp_ctx *ctx, double *dadd_lane_ops);
 
 /* Per-kernel launch counts and CUDA-event milliseconds accumulated since the last reset.
  * names: k1_score (regular rounds), k1_trace, k2_traceback, k3_pileup_vote, k5_final, k5_traceback, pack, other,

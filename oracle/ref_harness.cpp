@@ -11,7 +11,8 @@
 //   ALIGN   ref read qual                  sviper::map_single_read      (mapping.h:84-137)
 //   ROUND   fix flank ins_mean ins_sd n ref  then n lines "r1 q1 r2 q2"   one polish() round with profile dump
 //   POLISH  flank ins_mean ins_sd n ref      then n lines "r1 q1 r2 q2"   polish_to_perfection (polishing.h:319)
-//   FINAL   ref_part polished              convex-gap global alignment + CIGAR (sviper.h:452-466)
+//   FINAL   ref_part polished              convex-gap global alignment + CIGAR (sviper.h:452-466); polished = '@': the
+//                                          sequence the preceding POLISH returned
 //   EVAL    type pos end svlen k begin info cigar seq   assign_quality + refine_variant on the final record
 //                                                  (sviper.h:468-489, evaluate_final_mapping.h:17-28, variant.h:277-353)
 //   SUPPORT type pos svlen begin cigar         record_supports_variant on a long-read record (variant.h:239-275)
@@ -102,6 +103,7 @@ int main(int argc, char ** argv)
     if (argc < 2) { std::cerr << "usage: ref_harness cases.txt\n"; return 2; }
     std::ifstream in(argv[1]);
     std::string cmd;
+    Dna5String last_polished;
     while (in >> cmd)
     {
         if (cmd == "ALIGNX")
@@ -144,6 +146,7 @@ int main(int argc, char ** argv)
             if (cmd == "POLISH")
             {
                 Dna5String out = sviper::polish_to_perfection(r1, r2, h, config);
+                last_polished = out;
                 std::cout << "POLISH rounds=" << config.rounds << " subst=" << config.substituted_bases
                           << " ins=" << config.inserted_bases << " del=" << config.deleted_bases
                           << " baseQ_mean=" << hexd(config.baseQ_mean) << " mappQ_mean=" << hexd(config.mappQ_mean)
@@ -180,6 +183,7 @@ int main(int argc, char ** argv)
         {
             std::string a, b; in >> a >> b;
             Dna5String ref_part = a, polished = b;
+            if (b == "@") polished = last_polished;   // the output of the preceding POLISH (sviper.h:431 -> :457)
             sviper::CmdOptions opt; sviper::SViperConfig config{opt};
             Gaps<Dna5String, ArrayGaps> gapsRef(ref_part), gapsSeq(polished);
             double s = globalAlignment(gapsRef, gapsSeq, Score<double, Simple>(config.MM, config.MX, config.GE, config.GO),

@@ -70,7 +70,8 @@ EXPORTS = ["svp_create", "svp_destroy", "svp_last_error", "svp_version", "svp_al
            "svp_polish_batch", "svp_polish_rerun", "svp_final_align_batch", "svp_assign_quality", "svp_submit_polish", "svp_wait_any",
            "svp_debug_round", "svp_probe_dpx", "svp_stats", "svp_set_lanes", "svp_refine_variant", "svp_refine_info",
            "svp_format_quality", "svp_record_supports_variant", "svp_read_region_boundaries",
-           "svp_alignment_length_in_ref", "svp_cut_down_high_coverage", "svp_merge_record_group", "svp_k1_cells"]
+           "svp_alignment_length_in_ref", "svp_cut_down_high_coverage", "svp_merge_record_group", "svp_k1_cells",
+           "svp_flush", "svp_probe_fp64", "svp_engine_config", "svp_engine_stats", "svp_window_capacity"]
 
 _lib = None
 
@@ -101,9 +102,15 @@ def lib():
         L.svp_assign_quality.argtypes = [C.c_int32, C.c_int32]
         L.svp_submit_polish.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(WindowIn), C.POINTER(Result)]
         L.svp_wait_any.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.POINTER(Result))]
+        L.svp_flush.argtypes = [C.c_void_p]
+        L.svp_engine_config.argtypes = [C.c_void_p, C.c_int32, C.c_int32]
+        L.svp_engine_stats.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        L.svp_window_capacity.restype = C.c_int32
+        L.svp_window_capacity.argtypes = [C.c_int32]
         L.svp_debug_round.argtypes = [C.c_void_p, C.POINTER(WindowIn), C.c_int, f64p, u32p, u8p, C.c_int32, i32p, u8p,
                                       u8p, C.c_int32, i32p, f64p, u32p]
         L.svp_probe_dpx.argtypes = [C.c_void_p, f64p, f64p, f64p]
+        L.svp_probe_fp64.argtypes = [C.c_void_p, f64p]
         L.svp_stats.argtypes = [C.c_void_p, i32p, f64p, C.c_int]
         L.svp_set_lanes.argtypes = [C.c_void_p, C.c_int32]
         L.svp_refine_variant.argtypes = [C.c_int32, C.c_char_p, u32p, C.c_int32, C.POINTER(VariantPos), i32p]
@@ -342,7 +349,7 @@ class Context:
         keep = []
         n = len(variants)
         win = (WindowIn * n)(*[self.make_window(v, keep, with_final) for v in variants])
-        parts = [self.make_result(len(v["consensus"]) * 2 + 4096, keep) for v in variants]
+        parts = [self.make_result(self.L.svp_window_capacity(len(v["consensus"])), keep) for v in variants]
         res = (Result * n)(*[p[0] for p in parts])
         h2d = sum(len(k[0]) + len(k[2]) + len(k[3]) + len(k[5]) + len(k[6]) + (len(k[7]) if k[7] is not None else 0)
                   for k in keep if len(k) == 8)
@@ -351,12 +358,50 @@ class Context:
     def run_prepared(self, pb):
         self._check(self.L.svp_polish_batch(self.h, pb["n"], pb["win"], pb["res"]), "svp_polish_batch")
 
-    def collect(self, pb):
+    # ---- asynchronous scheduler (svp_submit_polish / svp_flush / svp_wait_any) -----------------------
+    def submit_prepared(self, pb, tag_base=0, flush=True):
+        """queues every variant of a prepared batch (tag = tag_base + index) and returns without waiting"""
+        for i in range(pb["n"]):
+            self._check(self.L.svp_submit_polish(self.h, tag_base + i, C.byref(pb["win"][i]), C.byref(pb["res"][i])),
+                        "svp_submit_polish")
+        if flush:
+            self._check(self.L.svp_flush(self.h), "svp_flush")
+
+    def wait_any(self):
+        """blocks for the next finished variant; returns its tag, or None when nothing is outstanding"""
+        tag = C.c_uint64(); r = C.POINTER(Result)()
+        rc = self.L.svp_wait_any(self.h, C.byref(tag), C.byref(r))
+        if rc == 1:
+            return None
+        self._check(rc, "svp_wait_any")
+        return tag.value
+
+    def wait_n(self, n):
+        tags = []
+        for _ in range(n):
+            t = self.wait_any()
+            if t is None:
+                raise RuntimeError("svp_wait_any: nothing outstanding after %d of %d results" % (len(tags), n))
+            tags.append(t)
+        return tags
+
+    def engine_config(self, batch_target=0, max_batch=0):
+        self._check(self.L.svp_engine_config(self.h, batch_target, max_batch), "svp_engine_config")
+
+    def engine_stats(self):
+        a, b = C.c_uint64(), C.c_uint64()
+        self._check(self.L.svp_engine_stats(self.h, C.byref(a), C.byref(b)), "svp_engine_stats")
+        return dict(batches=a.value, variants=b.value)
+
+    def collect(self, pb, allow_failed=False):
         out = []
         for i in range(pb["n"]):
             r = pb["res"][i]
             _, pol, cov, cop, ccnt = pb["parts"][i]
             if r.status != 0:
+                if allow_failed:
+                    out.append(dict(status=r.status))
+                    continue
                 raise RuntimeError("variant %d failed with status %d" % (i, r.status))
             d = dict(polished=pol[:r.polished_len].copy(), rounds=r.rounds, alignment_rounds=r.alignment_rounds, subst=r.substituted_bases,
                      ins=r.inserted_bases, dele=r.deleted_bases, mappQ_mean=r.mappQ_mean,
@@ -415,7 +460,11 @@ class Context:
     def probe_dpx(self):
         a, b, c = C.c_double(), C.c_double(), C.c_double()
         self._check(self.L.svp_probe_dpx(self.h, C.byref(a), C.byref(b), C.byref(c)), "svp_probe_dpx")
-        return dict(viaddmax=a.value, vimax3=b.value, mix=c.value)
+        d = dict(viaddmax=a.value, vimax3=b.value, mix=c.value)
+        e = C.c_double()
+        if self.L.svp_probe_fp64(self.h, C.byref(e)) == 0:
+            d["dadd"] = e.value
+        return d
 
     def k1_cells(self, reset=0, split=False):
         """DP cells computed by the score kernel for polish batches since the last reset (svp_k1_cells);

@@ -7,6 +7,8 @@
 #include <mutex>
 #include <thread>
 #include <cfloat>
+#include <condition_variable>
+#include <deque>
 #include <cub/device/device_scan.cuh>
 #include "ctx.cuh"
 #include "k1_score.cuh"
@@ -43,14 +45,14 @@ static int init_kernel_attrs(int device)
         return cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, want < 0 ? room : std::min(want, room)) ==
                cudaSuccess;
     };
-    bool ok = set_max((const void *)svp::k1_score_kernel<svp::K1_G, 19, false>, svp::K1Shape<svp::K1_G, 19>::SMEM_BYTES) &&
-              set_max((const void *)svp::k1_score_kernel<svp::K1_G, 32, false>, svp::K1Shape<svp::K1_G, 32>::SMEM_BYTES) &&
-              set_max((const void *)svp::k1_score_kernel<svp::K1_GW, 5, false>, svp::K1Shape<svp::K1_GW, 5>::SMEM_BYTES) &&
-              set_max((const void *)svp::k1_score_kernel<svp::K1_GW, 8, false>, svp::K1Shape<svp::K1_GW, 8>::SMEM_BYTES) &&
-              set_max((const void *)svp::k1_score_kernel<svp::K1_G, 19, true>, svp::K1Shape<svp::K1_G, 19>::SMEM_BYTES) &&
-              set_max((const void *)svp::k1_score_kernel<svp::K1_G, 32, true>, svp::K1Shape<svp::K1_G, 32>::SMEM_BYTES) &&
-              set_max((const void *)svp::k1_score_kernel<svp::K1_GW, 5, true>, svp::K1Shape<svp::K1_GW, 5>::SMEM_BYTES) &&
-              set_max((const void *)svp::k1_score_kernel<svp::K1_GW, 8, true>, svp::K1Shape<svp::K1_GW, 8>::SMEM_BYTES) &&
+    bool ok = set_max((const void *)svp::k1_score_kernel<svp::K1_G, 19, false, 128>, svp::K1Shape<svp::K1_G, 19>::SMEM_BYTES) &&
+              set_max((const void *)svp::k1_score_kernel<svp::K1_G, 32, false, 128>, svp::K1Shape<svp::K1_G, 32>::SMEM_BYTES) &&
+              set_max((const void *)svp::k1_score_kernel<svp::K1_GW, 5, false, 128>, svp::K1Shape<svp::K1_GW, 5>::SMEM_BYTES) &&
+              set_max((const void *)svp::k1_score_kernel<svp::K1_GW, 8, false, 128>, svp::K1Shape<svp::K1_GW, 8>::SMEM_BYTES) &&
+              set_max((const void *)svp::k1_score_kernel<svp::K1_G, 19, true, 128>, svp::K1Shape<svp::K1_G, 19>::SMEM_BYTES) &&
+              set_max((const void *)svp::k1_score_kernel<svp::K1_G, 32, true, 128>, svp::K1Shape<svp::K1_G, 32>::SMEM_BYTES) &&
+              set_max((const void *)svp::k1_score_kernel<svp::K1_GW, 5, true, 128>, svp::K1Shape<svp::K1_GW, 5>::SMEM_BYTES) &&
+              set_max((const void *)svp::k1_score_kernel<svp::K1_GW, 8, true, 128>, svp::K1Shape<svp::K1_GW, 8>::SMEM_BYTES) &&
               set_max((const void *)svp::k3_pileup_vote_kernel, -1) &&
               set_max((const void *)svp::k5_final_kernel<true>, -1);
     if (!ok) return SVP_ERR_CUDA;
@@ -100,7 +102,11 @@ static svp_ctx *make_ctx(int cuda_device, void *cuda_stream, bool is_lane)
         if (cudaStreamCreateWithFlags(&ctx->side[c], cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return nullptr; }
         cudaEventCreateWithFlags(&ctx->ev_side[c], cudaEventDisableTiming);
     }
-    if (cudaHostAlloc((void **)&ctx->h_active, 64, cudaHostAllocDefault) != cudaSuccess) { delete ctx; return nullptr; }
+    if (cudaHostAlloc((void **)&ctx->h_ctl, 2 * sizeof(svp::RoundCtl), cudaHostAllocDefault) != cudaSuccess) { delete ctx; return nullptr; }
+    memset(ctx->h_ctl, 0, 2 * sizeof(svp::RoundCtl));
+    for (int i = 0; i < 2; ++i) cudaEventCreateWithFlags(&ctx->ev_ctl[i], cudaEventDisableTiming);
+    if (const char *sr = getenv("SVP_SYNC_ROUNDS")) ctx->sync_rounds = atoi(sr) == 1;
+    if (const char *kt = getenv("SVP_K1_THREADS")) ctx->k1_threads = atoi(kt);
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) ctx->arena_budget = (size_t)(free_b * 0.6);
     const char *fw = getenv("SVP_FULL_WINDOW");
@@ -127,7 +133,15 @@ int svp_set_lanes(svp_ctx *ctx, int32_t n_lanes)
 void svp_destroy(svp_ctx *ctx)
 {
     if (!ctx) return;
-    cudaSetDevice(ctx->device);
+    engine_stop(ctx);
+    if (cudaSetDevice(ctx->device) == cudaErrorCudartUnloading)
+    {
+        // process exit: the CUDA runtime is already gone (a context held by a static object); nothing left to free
+        for (svp_ctx *l : ctx->lanes) delete l;
+        delete ctx->resident;
+        delete ctx;
+        return;
+    }
     cudaStreamSynchronize(ctx->stream);
     for (svp_ctx *l : ctx->lanes) svp_destroy(l);
     ctx->lanes.clear();
@@ -143,9 +157,12 @@ void svp_destroy(svp_ctx *ctx)
                       &ctx->fcig_out, &ctx->gapstep, &ctx->edge};
     for (DevBuf *b : bufs) b->release();
     ctx->cons_init.release(); ctx->states_init.release();
-    ctx->win_done.release(); ctx->active.release(); ctx->gather_desc.release(); ctx->gather_out.release();
+    ctx->win_done.release(); ctx->ctl.release(); ctx->gather_desc.release(); ctx->gather_out.release();
+    ctx->fail19.release(); ctx->fail32.release(); ctx->sstate.release(); ctx->reg19.release(); ctx->reg32.release();
+    ctx->mix19.release(); ctx->mix32.release(); ctx->mixcnt.release(); ctx->edit.release(); ctx->emax.release();
+    for (int i = 0; i < 2; ++i) if (ctx->ev_ctl[i]) cudaEventDestroy(ctx->ev_ctl[i]);
     ctx->stage.release();
-    if (ctx->h_active) cudaFreeHost(ctx->h_active);
+    if (ctx->h_ctl) cudaFreeHost(ctx->h_ctl);
     delete ctx->resident;
     for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
     cudaEventDestroy(ctx->ev0);
@@ -191,7 +208,7 @@ int svp_align_batch(svp_ctx *ctx, const svp_align_in *in, svp_align_out *out, in
     int64_t *E = nullptr;
     if (with_traceback)
     {
-        rc = run_trace_pass(ctx, nullptr, false);
+        rc = run_trace_pass_checked(ctx, nullptr, false);
         if (rc) return rc;
         al = ctx->stage.get<svp::AlnOut>(n);
         if (!al) return svp_fail_msg(ctx, SVP_ERR_CUDA, "cannot allocate pinned staging memory");
@@ -240,7 +257,7 @@ int svp_align_rerun(svp_ctx *ctx, int with_traceback, float *kernel_ms)
     ctx->timing = t;
     if (rc) return rc;
     CK(cudaEventRecord(ctx->ev1, ctx->stream));
-    if (with_traceback) { rc = run_trace_pass(ctx, nullptr, false); if (rc) return rc; }
+    if (with_traceback) { rc = run_trace_pass_checked(ctx, nullptr, false); if (rc) return rc; }
     CK(cudaStreamSynchronize(ctx->stream));
     if (kernel_ms) CK(cudaEventElapsedTime(kernel_ms, ctx->ev0, ctx->ev1));
     return SVP_OK;
@@ -271,6 +288,28 @@ int svp_probe_dpx(svp_ctx *ctx, double *viaddmax_lane_ops, double *vimax3_lane_o
         }
         if (outs[mode]) *outs[mode] = (double)blocks * threads * iters * ops_per_iter[mode] / (best * 1e-3);
     }
+    o.release();
+    return SVP_OK;
+}
+
+int svp_probe_fp64(svp_ctx *ctx, double *dadd_lane_ops)
+{
+    if (!ctx || !dadd_lane_ops) return SVP_ERR_ARG;
+    CK(cudaSetDevice(ctx->device));
+    const int blocks = 148 * 8, threads = 256, iters = 2048;
+    DevBuf o; CK(o.ensure((size_t)blocks * threads * 8));
+    float best = 1e30f;
+    for (int rep = 0; rep < 4; ++rep)
+    {
+        CK(cudaEventRecord(ctx->ev0, ctx->stream));
+        svp::dadd_probe_kernel<<<blocks, threads, 0, ctx->stream>>>(o.as<double>(), iters, 1.0000001);
+        CK(cudaGetLastError());
+        CK(cudaEventRecord(ctx->ev1, ctx->stream));
+        CK(cudaEventSynchronize(ctx->ev1));
+        float ms = 0; CK(cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+        if (rep > 0 && ms < best) best = ms;
+    }
+    *dadd_lane_ops = (double)blocks * threads * iters * 8.0 / (best * 1e-3);
     o.release();
     return SVP_OK;
 }

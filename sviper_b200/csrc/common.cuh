@@ -50,6 +50,18 @@ struct TracePlan
     int32_t dlo;          // band: lowest diagonal j - i
     int32_t pad_;
 };
+// Device-resident control block of one pass (one per context): what the round needs from the per-round arenas and
+// what is left to do. Written by fit_kernel / count_active_kernel, copied to pinned host memory once per round; the
+// host reads it one round LATE (the next round is already queued), so no kernel launch waits for a host round trip.
+struct RoundCtl
+{
+    int32_t ovf;                      // != 0: an arena is too small: traced pass, traceback and vote skip the round (no state changes)
+    int32_t round;
+    int64_t need_units, need_words;   // record / path units and trace words this round needs
+    int32_t cls[4];                   // tasks per traced-pass class
+    int32_t active, live_pairs;       // windows still being polished, their read pairs
+};
+
 // traced-pass classes (plan_kernel bins tasks by band width)
 enum { TC_BAND16 = 0, TC_BAND32 = 1, TC_STRIP5 = 2, TC_STRIP8 = 3, TC_N = 4 };
 }  // namespace svp

@@ -93,6 +93,7 @@ struct DevSeqs
 
 struct PolishLayout;
 struct FinalSpec;
+struct svp_engine;
 
 constexpr int SVP_DEFAULT_LANES = 4, SVP_MAX_LANES = 16, SVP_MIN_PER_LANE = 4;
 
@@ -129,14 +130,15 @@ struct svp_ctx
     DevBuf task_read, task_win, task_idx19, task_idx32;
     DevBuf task_mate, win_ins;              // polish batches: mate task per task (-1 none), (insert mean, sd) per window
     bool prune_pairs = false;               // run_trace_pass: skip the traceback of pairs that cannot be proper
-    int ntasks = 0, n19 = 0, n32 = 0;
+    int ntasks = 0, n19 = 0, n32 = 0, n_short = 0, n_long = 0;   // tasks; by score-kernel class (<= 152 / longer rows); by strip class (<= 160)
     DevBuf score_out, plans, units, E, tunits, TE, cls_count, cls_list, scan_tmp, trace, ops, alns;
     DevBuf rec_code, rec_qual, rec_inslen, rec_insq;
     int64_t E_total = 0;
     // ---- polish pipeline ----
     DevBuf descs, states, states_init, pair_task, cons0, cons1, inslen, voff, profile, cov, isgap, decision, proper, cons_init;
     // strand certificates (k1_score.cuh, K1Mix): per-task strand state, per-round task lists, per-window edit density
-    DevBuf sstate, reg19, reg32, mix19, mix32, mixcnt, edit, emax;
+    DevBuf sstate, reg19, reg32, mix19, mix32, fail19, fail32, mixcnt, edit, emax;
+    int k1_threads = 0;                     // 0: choose per launch; 64 / 128: force the block size of the throughput shape (SVP_K1_THREADS)
     bool mixcnt_zeroed = false;             // mixcnt: 4 list counters (reset every round) + the DP cell counter at byte 32
     int64_t pairs_total = 0, n_mateless = 0;   // pairs of the batch; pairs with a dummy mate
     bool mixed_rounds = true;               // SVP_NO_MIXED=1 turns the mixed tasks off (A/B measurements)
@@ -147,13 +149,17 @@ struct svp_ctx
     int table_size = 0;
     // ---- host staging / result gather ----
     HostStage stage;
-    DevBuf win_done, active, gather_desc, gather_out;
-    int32_t *h_active = nullptr;   // pinned flag the round loop polls
-    // ---- scheduler facade ----
-    std::vector<uint64_t> q_tag;
-    std::vector<const svp_window_in *> q_in;
-    std::vector<svp_result *> q_out;
-    size_t q_done = 0, q_ready = 0;
+    DevBuf win_done, gather_desc, gather_out;
+    // ---- round control: device block + two pinned copies (read one round late) ----
+    DevBuf ctl;
+    svp::RoundCtl *h_ctl = nullptr;          // pinned, 2 slots
+    cudaEvent_t ev_ctl[2] = {nullptr, nullptr};
+    int64_t cap_units = 0, cap_words = 0;   // what the per-round arenas (records, paths, trace) currently hold
+    int n_regrow = 0;                       // rounds repeated because an arena had to grow
+    bool sync_rounds = false;               // SVP_SYNC_ROUNDS=1: wait for every round before queueing the next (A/B switch)
+    int64_t est_units = 0, est_words = 0;   // first-round estimate of the current batch (polish_upload / upload_tasks)
+    // ---- asynchronous batch scheduler (api_final.inc): one worker thread per lane ----
+    struct svp_engine *engine = nullptr;
 };
 
 static int svp_fail(svp_ctx *ctx, cudaError_t e, const char *what, const char *file, int line)
@@ -217,15 +223,16 @@ __global__ void window_refresh_kernel(const VarDesc *__restrict__ descs, const V
     win_done[v] = states[v].done ? 1 : 0;
 }
 
-// out[0] = variants still being polished, out[1] = their read pairs (an upper bound of half the live tasks)
+// ctl->active = variants still being polished, ctl->live_pairs = their read pairs (an upper bound of half the live tasks);
+// both were zeroed by fit_kernel earlier in the round
 __global__ void count_active_kernel(const VarDesc *__restrict__ descs, const VarState *__restrict__ states, int nv,
-                                    int32_t *__restrict__ out)
+                                    RoundCtl *__restrict__ ctl)
 {
     int v = blockIdx.x * blockDim.x + threadIdx.x;
     int a = (v < nv) ? !states[v].done : 0;
-    if (a) atomicAdd(out + 1, descs[v].n_pairs);
+    if (a) atomicAdd(&ctl->live_pairs, descs[v].n_pairs);
     a = __syncthreads_count(a);
-    if (threadIdx.x == 0 && a) atomicAdd(out, a);
+    if (threadIdx.x == 0 && a) atomicAdd(&ctl->active, a);
 }
 
 // DPX probe: independent dependent-chains per thread, enough threads to fill the chip
@@ -255,6 +262,23 @@ __global__ void dpx_probe_kernel(uint32_t *out, int iters)
     uint32_t r = 0;
 #pragma unroll
     for (int i = 0; i < 8; ++i) r ^= a[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = r;
+}
+
+// fp64 add probe: 8 independent chains per thread
+__global__ void dadd_probe_kernel(double *out, int iters, double inc)
+{
+    double a[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) a[i] = (double)threadIdx.x + i;
+    for (int it = 0; it < iters; ++it)
+    {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) a[i] = __dadd_rn(a[i], inc);
+    }
+    double r = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) r += a[i];
     out[blockIdx.x * blockDim.x + threadIdx.x] = r;
 }
 }  // namespace svp

@@ -29,15 +29,16 @@ constexpr int K1_G = 8;                // lanes per task of the throughput shape
 constexpr int K1_GW = 32;              // lanes per task of the WIDE shape: a third of the steps per task, more
                                        // per-step overhead. Used when few tasks are left (tail rounds), where the
                                        // kernel's duration is the latency of one task, not the chip's throughput.
-constexpr int K1_THREADS = 128;
+constexpr int K1_THREADS = 128;         // default block size; launches of less than ~2 waves use 64-thread blocks (8 tasks),
+                                        // which spread an uneven number of blocks more evenly over the 148 SMs
 constexpr int K1_BIAS = 0x2000;
 
 __host__ __device__ constexpr uint32_t k1_pk(int x) { return (uint32_t)((K1_BIAS + x) & 0xffff) * 0x00010001u; }
 
-template <int G, int RPL>
+template <int G, int RPL, int THREADS = K1_THREADS>
 struct K1Shape
 {
-    static constexpr int TASKS_PER_BLOCK = K1_THREADS / G;
+    static constexpr int TASKS_PER_BLOCK = THREADS / G;
     static constexpr int NSLOT = G * RPL;
     // a lane's RPL profile entries of one window character are contiguous (fetched with LDS.128); the lane
     // stride KPAD is a multiple of 4 words with KPAD/4 odd, so the 8 lanes of a task (= one quarter-warp, the
@@ -66,7 +67,7 @@ struct K1Mix
     const int32_t *n_dev;      // number of tasks (pairs if MIXED) of this launch, on the device; null: `ntasks`
     int32_t *sstate;           // per task: bit 0 strand known, bit 1 is_rc, bits 16..31 bound on the other strand's score
     const int32_t *emax;       // per window: edit cost E for W = 320, W = 512
-    int32_t *fb19, *fb32;      // regular lists the failures are appended to
+    int32_t *fb19, *fb32;      // lists the failed certificates are appended to (both strands again, same round)
     int32_t *fb_cnt;           // their counters [2]
     unsigned long long *cells; // DP cells computed (statistics)
 };
@@ -76,8 +77,8 @@ __device__ __forceinline__ uint32_t k1_pk2(int a, int b)
     return (uint32_t)((K1_BIAS + a) & 0xffff) | ((uint32_t)((K1_BIAS + b) & 0xffff) << 16);
 }
 
-template <int G, int RPL, bool MIXED>
-__global__ void __launch_bounds__(K1_THREADS, 4) k1_score_kernel(const int32_t *__restrict__ task_read,
+template <int G, int RPL, bool MIXED, int THREADS>
+__global__ void __launch_bounds__(THREADS, 512 / THREADS) k1_score_kernel(const int32_t *__restrict__ task_read,
                                                        const int32_t *__restrict__ task_win,
                                                        const int32_t *__restrict__ task_idx, int ntasks,
                                                        const uint8_t *__restrict__ win_done,
@@ -87,7 +88,7 @@ __global__ void __launch_bounds__(K1_THREADS, 4) k1_score_kernel(const int32_t *
                                                        ScoreOut *__restrict__ out,
                                                        uint32_t one /* always 1; opaque to the compiler */, K1Mix mix)
 {
-    using Sh = K1Shape<G, RPL>;
+    using Sh = K1Shape<G, RPL, THREADS>;
     constexpr int NSLOT = Sh::NSLOT, PST = Sh::PST, KPAD = Sh::KPAD, NQ = (RPL + 3) / 4;
     extern __shared__ uint32_t k1_smem[];
     const int g = threadIdx.x & (G - 1), grp = threadIdx.x / G;

@@ -126,6 +126,19 @@ __global__ void plan_kernel(const int32_t *__restrict__ task_read, const int32_t
     cls_list[(size_t)cls * ntasks + at] = t;
 }
 
+// After the scans: does the round fit its arenas? (E_end / TE_end: totals of the exclusive scans)
+__global__ void fit_kernel(const int64_t *__restrict__ E_end, const int64_t *__restrict__ TE_end,
+                           const int32_t *__restrict__ cls_count, RoundCtl *__restrict__ ctl, int round, int64_t cap_units,
+                           int64_t cap_words)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    const int64_t nu = *E_end, nw = *TE_end;
+    ctl->need_units = nu; ctl->need_words = nw; ctl->round = round;
+    for (int c = 0; c < TC_N; ++c) ctl->cls[c] = cls_count[c];
+    ctl->active = 0; ctl->live_pairs = 0;
+    ctl->ovf = (nu > cap_units || nw > cap_words) ? 1 : 0;
+}
+
 template <int RPL>
 struct KTShape
 {
@@ -135,7 +148,8 @@ struct KTShape
 };
 
 template <int RPL>
-__global__ void __launch_bounds__(KT_WARPS * 32, 6) k1_trace_kernel(const TracePlan *__restrict__ plans, int ntasks,
+__global__ void __launch_bounds__(KT_WARPS * 32, 6) k1_trace_kernel(const TracePlan *__restrict__ plans,
+                                                                const RoundCtl *__restrict__ ctl, int cls,
                                                                 const int32_t *__restrict__ task_idx,
                                                                 SeqStore reads, SeqStore wins,
                                                                 const int64_t *__restrict__ E,
@@ -146,8 +160,8 @@ __global__ void __launch_bounds__(KT_WARPS * 32, 6) k1_trace_kernel(const TraceP
     extern __shared__ int32_t kt_smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int slot = blockIdx.x * KT_WARPS + warp;
-    if (slot >= ntasks) return;
-    const int task = task_idx ? task_idx[slot] : slot;
+    if (ctl->ovf || slot >= ctl->cls[cls]) return;     // the grid is sized for an upper bound of the class
+    const int task = task_idx[slot];
     int32_t *prof = kt_smem + warp * Sh::PROF_WORDS;   // prof[c][k][lane]
     const TracePlan pl = plans[task];
     const int ncols = pl.ncols;
@@ -249,7 +263,8 @@ constexpr int KB_WMAX = SVP_MAX_READ_LEN + 2 * KB_MAXW32 + 8;   // staged window
 constexpr int KB_SEQ_BYTES = KB_RMAX + KB_WMAX + 8;
 
 template <int LPA, int DPL>
-__global__ void __launch_bounds__(KB_THREADS, 6) k1_band_kernel(const TracePlan *__restrict__ plans, int ntasks,
+__global__ void __launch_bounds__(KB_THREADS, 6) k1_band_kernel(const TracePlan *__restrict__ plans,
+                                                            const RoundCtl *__restrict__ ctl, int cls,
                                                             const int32_t *__restrict__ task_idx, SeqStore reads,
                                                             SeqStore wins, const int64_t *__restrict__ TE,
                                                             uint32_t *__restrict__ trace)
@@ -261,6 +276,8 @@ __global__ void __launch_bounds__(KB_THREADS, 6) k1_band_kernel(const TracePlan 
     const int l = threadIdx.x % LPA, grp = threadIdx.x / LPA;
     const int slot = blockIdx.x * APB + grp;
     const unsigned gmask = (LPA == 32) ? 0xffffffffu : (((1u << (LPA & 31)) - 1u) << (LPA * ((threadIdx.x & 31) / LPA)));
+    const int ntasks = ctl->ovf ? 0 : ctl->cls[cls];    // the grid is sized for an upper bound of the class
+    if (blockIdx.x * APB >= ntasks) return;             // (whole block)
     const bool live = slot < ntasks;
     int R = 0, e = 0, dlo = 0, rc = 0, runit = 0, wunit = 0, jbase = 0;
     uint32_t *tr = trace;
@@ -453,13 +470,13 @@ struct RecArrays
 constexpr int K2_WARPS = 4;
 
 __global__ void __launch_bounds__(K2_WARPS * 32, 6) k2_traceback_kernel(
-    const TracePlan *__restrict__ plans, int ntasks, SeqStore reads, SeqStore wins,
+    const TracePlan *__restrict__ plans, const RoundCtl *__restrict__ ctl, int ntasks, SeqStore reads, SeqStore wins,
     const uint8_t *__restrict__ read_quals, const int64_t *__restrict__ qual_off,
     const uint32_t *__restrict__ trace, uint8_t *__restrict__ ops_buf, RecArrays rec,
     const int64_t *__restrict__ E, const int64_t *__restrict__ TE, AlnOut *__restrict__ out)
 {
     const int t = blockIdx.x * K2_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-    if (t >= ntasks) return;
+    if (t >= ntasks || ctl->ovf) return;
     const TracePlan pl = plans[t];
     if (pl.ncols == -2)
     {

@@ -85,9 +85,11 @@ __global__ void __launch_bounds__(K3_THREADS) k3_pileup_vote_kernel(
     const VarDesc *__restrict__ descs, VarState *__restrict__ states, const int32_t *__restrict__ pair_task,
     const AlnOut *__restrict__ alns, const TracePlan *__restrict__ plans, RecArrays rec,
     const int64_t *__restrict__ rec_off, SeqStore reads, const uint8_t *__restrict__ read_quals,
-    const int64_t *__restrict__ qual_off, K3Buffers buf, int force_single_round, int max_pairs)
+    const int64_t *__restrict__ qual_off, K3Buffers buf, int force_single_round, int max_pairs,
+    const RoundCtl *__restrict__ ctl)
 {
     const int v = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (ctl->ovf) return;   // the round's alignments were not produced (arena too small): it is repeated, nothing may change
     VarState st = states[v];
     if (st.done) return;
     const VarDesc d = descs[v];

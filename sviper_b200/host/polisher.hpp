@@ -18,6 +18,7 @@
 #include <condition_variable>
 #include <cstdint>
 #include <cstring>
+#include <deque>
 #include <functional>
 #include <future>
 #include <memory>
@@ -93,6 +94,7 @@ inline void compute_baseQ_stats(Config & cfg, std::vector<QRead> const & reads1,
                 if (ord_value(r.seq[i]) == 4) q = 0;
                 sum += q;
             }
+    if (reads1.empty()) return;   // polishing.h:201-202: nothing to average, baseQ_mean untouched
     double den = 0;
     if (!reads1.empty()) den += (double)reads1.size() * (double)reads1[0].seq.size();
     if (!reads2.empty()) den += (double)reads2.size() * (double)reads2[0].seq.size();
@@ -203,7 +205,8 @@ struct ResultBuffers
     svp_result res;
 
     explicit ResultBuffers(size_t consensus_len, int cigar_cap = 4096)
-        : polished(2 * consensus_len + 4096), cov(3 * (consensus_len + consensus_len / 4 + 512) + 1024),
+        : polished((size_t)svp_window_capacity((int32_t)consensus_len)),
+          cov(3 * (size_t)svp_window_capacity((int32_t)consensus_len) + 1024),
           cig_cnt(cigar_cap), cig_op(cigar_cap)
     {
         std::memset(&res, 0, sizeof res);
@@ -354,20 +357,24 @@ private:
                 // leave work for the other GPUs: take at most an even share of what is queued
                 size_t take = (queue_.size() + polishers_.size() - 1) / polishers_.size();
                 if (take > max_batch_) take = max_batch_;
-                for (size_t i = 0; i < take; ++i) { batch.push_back(std::move(queue_.front())); queue_.erase(queue_.begin()); }
+                for (size_t i = 0; i < take; ++i) { batch.push_back(std::move(queue_.front())); queue_.pop_front(); }
                 if (!queue_.empty()) cv_.notify_all();
             }
             std::vector<PackedVariant *> in;
             std::vector<ResultBuffers *> out;
             for (auto & j : batch) { in.push_back(j->in.get()); out.push_back(j->out.get()); }
-            try
+            std::exception_ptr failed;
+            try { polishers_[g]->polish_batch(in, out); }
+            catch (...) { failed = std::current_exception(); }
+            // every promise is settled exactly once; a throwing set_value must not take the worker down
+            for (auto & j : batch)
             {
-                polishers_[g]->polish_batch(in, out);
-                for (auto & j : batch) j->done.set_value(std::move(j->out));
-            }
-            catch (...)
-            {
-                for (auto & j : batch) j->done.set_exception(std::current_exception());
+                try
+                {
+                    if (failed) j->done.set_exception(failed);
+                    else j->done.set_value(std::move(j->out));
+                }
+                catch (std::future_error const &) {}
             }
         }
     }
@@ -376,7 +383,7 @@ private:
     unsigned linger_us_;
     std::vector<std::unique_ptr<Polisher>> polishers_;
     std::vector<std::thread> workers_;
-    std::vector<std::unique_ptr<Job>> queue_;
+    std::deque<std::unique_ptr<Job>> queue_;
     std::mutex m_;
     std::condition_variable cv_;
     bool stop_ = false;

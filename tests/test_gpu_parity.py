@@ -247,27 +247,74 @@ def test_final_golden_and_random(ctx):
         assert sc == g["score"] and orc.cigar(ops) == g["cigar"]
 
 
-def test_scheduler_facade(ctx):
-    """svp_submit_polish / svp_wait_any return the same results as one svp_polish_batch"""
-    import ctypes as C
+def test_async_scheduler(ctx):
+    """svp_submit_polish / svp_flush / svp_wait_any (asynchronous submissions with an explicit wait) return the
+    same results as one svp_polish_batch, whatever device batches the lanes form: several submissions in flight,
+    small batch targets, waiting threads"""
+    import threading
+    vs = [rc.small_variant(300 + s) for s in range(23)]
+    for v in vs:
+        v["ref_part"] = v["truth"]
+    want = ctx.polish_batch(vs, with_final=True)
+    assert ctx.wait_any() is None                          # nothing outstanding
+    # (a) everything queued, one flush
+    pb = ctx.prepare(vs, True)
+    ctx.submit_prepared(pb, tag_base=1000)
+    assert sorted(ctx.wait_n(len(vs))) == list(range(1000, 1000 + len(vs))) and ctx.wait_any() is None
+    for g, w in zip(ctx.collect(pb), want):
+        assert np.array_equal(g["polished"], w["polished"]) and g["cigar"] == w["cigar"] and g["rounds"] == w["rounds"]
+        assert np.array_equal(g["cov"], w["cov"]) and g["final_score"] == w["final_score"]
+    # (b) a small batch target: the lanes start while the submitter is still queueing; a second thread waits
+    ctx.engine_config(batch_target=3)
+    before = ctx.engine_stats()
+    pb = ctx.prepare(vs, True)
+    tags = []
+    th = threading.Thread(target=lambda: tags.extend(ctx.wait_n(len(vs))))
+    ctx.submit_prepared(pb, tag_base=0, flush=False)
+    th.start()                                             # the waiter flushes what is left
+    th.join(timeout=120)
+    assert not th.is_alive() and sorted(tags) == list(range(len(vs)))
+    st = ctx.engine_stats()
+    assert st["variants"] - before["variants"] == len(vs) and st["batches"] - before["batches"] >= 2
+    for g, w in zip(ctx.collect(pb), want):
+        assert np.array_equal(g["polished"], w["polished"]) and g["cigar"] == w["cigar"]
+    ctx.engine_config(batch_target=256)
+
+
+def test_round_loop_variants_agree(ctx, monkeypatch):
+    """The round loop queues round r + 1 before it has seen the outcome of round r, and sizes the per-round arenas from an
+    estimate. Neither may change a result: (a) SVP_SYNC_ROUNDS=1 waits for every round; (b) SVP_SMALL_ARENAS=1 starts from
+    arenas that are far too small, so the first round of every batch overflows, leaves the state untouched and is repeated
+    after the arenas have grown (RoundCtl::ovf); (c) 64- and 128-thread blocks of the score kernel."""
     from sviper_b200 import api
-    vs = [rc.small_variant(300 + s) for s in range(3)]
-    want = ctx.polish_batch(vs, with_final=False)
-    keep, wins, ress = [], [], []
-    for i, v in enumerate(vs):
-        w = api.Context.make_window(v, keep, with_final=False)
-        r = api.Context.make_result(len(v["consensus"]) * 2 + 4096, keep)
-        wins.append(w); ress.append(r)
-        assert ctx.L.svp_submit_polish(ctx.h, 1000 + i, C.byref(w), C.byref(r[0])) == 0
-    seen = []
-    while True:
-        tag = C.c_uint64(); rp = C.POINTER(api.Result)()
-        rc_ = ctx.L.svp_wait_any(ctx.h, C.byref(tag), C.byref(rp))
-        if rc_ == 1:
-            break
-        assert rc_ == 0
-        i = tag.value - 1000
-        seen.append(i)
-        assert np.array_equal(ress[i][1][:rp.contents.polished_len], want[i]["polished"])
-        assert rp.contents.rounds == want[i]["rounds"]
-    assert sorted(seen) == [0, 1, 2]
+    vs = [rc.small_variant(900 + s, n_pairs=30 + 7 * s) for s in range(9)]
+    for v in vs:
+        v["ref_part"] = v["truth"]
+    want = ctx.polish_batch(vs, with_final=True)
+
+    def same(got):
+        for g, w in zip(got, want):
+            assert np.array_equal(g["polished"], w["polished"]) and g["cigar"] == w["cigar"] and g["rounds"] == w["rounds"]
+            assert np.array_equal(g["cov"], w["cov"]) and (g["subst"], g["ins"], g["dele"]) == (w["subst"], w["ins"], w["dele"])
+
+    monkeypatch.setenv("SVP_SYNC_ROUNDS", "1")
+    c = api.Context(0)
+    same(c.polish_batch(vs, with_final=True))
+    c.close()
+    monkeypatch.delenv("SVP_SYNC_ROUNDS")
+    for lanes in (1, 2):
+        c = api.Context(0)
+        c.set_lanes(lanes)
+        monkeypatch.setenv("SVP_SMALL_ARENAS", "1")
+        same(c.polish_batch(vs, with_final=True))
+        r = c.align_batch([v["reads1"][0] for v in vs], [v["consensus"] for v in vs], np.arange(9), np.arange(9), ops_cap=700)
+        monkeypatch.delenv("SVP_SMALL_ARENAS")
+        r2 = ctx.align_batch([v["reads1"][0] for v in vs], [v["consensus"] for v in vs], np.arange(9), np.arange(9), ops_cap=700)
+        assert r["ops"] == r2["ops"] and np.array_equal(r["lead"], r2["lead"])
+        c.close()
+    for kt in ("64", "128"):
+        monkeypatch.setenv("SVP_K1_THREADS", kt)
+        c = api.Context(0)
+        same(c.polish_batch(vs, with_final=True))
+        c.close()
+    monkeypatch.delenv("SVP_K1_THREADS")
