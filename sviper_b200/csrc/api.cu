@@ -45,14 +45,18 @@ static int init_kernel_attrs(int device)
         return cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, want < 0 ? room : std::min(want, room)) ==
                cudaSuccess;
     };
-    bool ok = set_max((const void *)svp::k1_score_kernel<svp::K1_G, 19, false, 128>, svp::K1Shape<svp::K1_G, 19>::SMEM_BYTES) &&
-              set_max((const void *)svp::k1_score_kernel<svp::K1_G, 32, false, 128>, svp::K1Shape<svp::K1_G, 32>::SMEM_BYTES) &&
+    bool ok = set_max((const void *)svp::k1_score_kernel<svp::K1_G, 19, false, 128>, -1) &&
+              set_max((const void *)svp::k1_score_kernel<svp::K1_G, 32, false, 128>, -1) &&
               set_max((const void *)svp::k1_score_kernel<svp::K1_GW, 5, false, 128>, svp::K1Shape<svp::K1_GW, 5>::SMEM_BYTES) &&
               set_max((const void *)svp::k1_score_kernel<svp::K1_GW, 8, false, 128>, svp::K1Shape<svp::K1_GW, 8>::SMEM_BYTES) &&
-              set_max((const void *)svp::k1_score_kernel<svp::K1_G, 19, true, 128>, svp::K1Shape<svp::K1_G, 19>::SMEM_BYTES) &&
-              set_max((const void *)svp::k1_score_kernel<svp::K1_G, 32, true, 128>, svp::K1Shape<svp::K1_G, 32>::SMEM_BYTES) &&
+              set_max((const void *)svp::k1_score_kernel<svp::K1_G, 19, true, 128>, -1) &&
+              set_max((const void *)svp::k1_score_kernel<svp::K1_G, 32, true, 128>, -1) &&
               set_max((const void *)svp::k1_score_kernel<svp::K1_GW, 5, true, 128>, svp::K1Shape<svp::K1_GW, 5>::SMEM_BYTES) &&
               set_max((const void *)svp::k1_score_kernel<svp::K1_GW, 8, true, 128>, svp::K1Shape<svp::K1_GW, 8>::SMEM_BYTES) &&
+              set_max((const void *)svp::k1_score_kernel<svp::K1_G, 19, false, 64>, -1) &&
+              set_max((const void *)svp::k1_score_kernel<svp::K1_G, 32, false, 64>, -1) &&
+              set_max((const void *)svp::k1_score_kernel<svp::K1_G, 19, true, 64>, -1) &&
+              set_max((const void *)svp::k1_score_kernel<svp::K1_G, 32, true, 64>, -1) &&
               set_max((const void *)svp::k3_pileup_vote_kernel, -1) &&
               set_max((const void *)svp::k5_final_kernel<true>, -1);
     if (!ok) return SVP_ERR_CUDA;
@@ -105,7 +109,7 @@ static svp_ctx *make_ctx(int cuda_device, void *cuda_stream, bool is_lane)
     if (cudaHostAlloc((void **)&ctx->h_ctl, 2 * sizeof(svp::RoundCtl), cudaHostAllocDefault) != cudaSuccess) { delete ctx; return nullptr; }
     memset(ctx->h_ctl, 0, 2 * sizeof(svp::RoundCtl));
     for (int i = 0; i < 2; ++i) cudaEventCreateWithFlags(&ctx->ev_ctl[i], cudaEventDisableTiming);
-    if (const char *sr = getenv("SVP_SYNC_ROUNDS")) ctx->sync_rounds = atoi(sr) == 1;
+    if (const char *sr = getenv("SVP_SPECULATIVE_ROUNDS")) ctx->sync_rounds = atoi(sr) != 1;
     if (const char *kt = getenv("SVP_K1_THREADS")) ctx->k1_threads = atoi(kt);
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) ctx->arena_budget = (size_t)(free_b * 0.6);

@@ -156,7 +156,7 @@ struct svp_ctx
     cudaEvent_t ev_ctl[2] = {nullptr, nullptr};
     int64_t cap_units = 0, cap_words = 0;   // what the per-round arenas (records, paths, trace) currently hold
     int n_regrow = 0;                       // rounds repeated because an arena had to grow
-    bool sync_rounds = false;               // SVP_SYNC_ROUNDS=1: wait for every round before queueing the next (A/B switch)
+    bool sync_rounds = true;                // wait for the outcome of a round before queueing the next (SVP_SPECULATIVE_ROUNDS=1: one round ahead)
     int64_t est_units = 0, est_words = 0;   // first-round estimate of the current batch (polish_upload / upload_tasks)
     // ---- asynchronous batch scheduler (api_final.inc): one worker thread per lane ----
     struct svp_engine *engine = nullptr;

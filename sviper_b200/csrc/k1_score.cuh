@@ -32,6 +32,9 @@ constexpr int K1_GW = 32;              // lanes per task of the WIDE shape: a th
 constexpr int K1_THREADS = 128;         // default block size; launches of less than ~2 waves use 64-thread blocks (8 tasks),
                                         // which spread an uneven number of blocks more evenly over the 148 SMs
 constexpr int K1_BIAS = 0x2000;
+constexpr int K1_WEAK = 24;             // reads whose best strand scores below this (mostly reads hanging off a window edge,
+                                        // score < 0: the certificate needs S >= 0) are not tried as mixed tasks in the next
+                                        // round: they go to the regular list up front, which runs BESIDE the mixed launch
 
 __host__ __device__ constexpr uint32_t k1_pk(int x) { return (uint32_t)((K1_BIAS + x) & 0xffff) * 0x00010001u; }
 
@@ -65,7 +68,8 @@ struct K1Shape
 struct K1Mix
 {
     const int32_t *n_dev;      // number of tasks (pairs if MIXED) of this launch, on the device; null: `ntasks`
-    int32_t *sstate;           // per task: bit 0 strand known, bit 1 is_rc, bits 16..31 bound on the other strand's score
+    int32_t *sstate;           // per task: bit 0 strand known, bit 1 is_rc, bit 2 weak (winner scored < K1_WEAK: its certificate
+                               // would probably fail again), bits 16..31 bound on the other strand's score
     const int32_t *emax;       // per window: edit cost E for W = 320, W = 512
     int32_t *fb19, *fb32;      // lists the failed certificates are appended to (both strands again, same round)
     int32_t *fb_cnt;           // their counters [2]
@@ -276,7 +280,8 @@ __global__ void __launch_bounds__(THREADS, 512 / THREADS) k1_score_kernel(const 
                 const int rc = !(s_lo > s_hi);                       // mapping.h:121
                 int lose = rc ? s_lo : s_hi;
                 lose = max(-32768, min(32767, lose));
-                mix.sstate[task] = (int32_t)(((uint32_t)lose << 16) | (uint32_t)(rc << 1) | 1u);
+                const int win = rc ? s_hi : s_lo;
+                mix.sstate[task] = (int32_t)(((uint32_t)lose << 16) | (uint32_t)(rc << 1) | 1u | (win < K1_WEAK ? 4u : 0u));
             }
             if (mix.cells) atomicAdd(mix.cells, 2ull * (unsigned long long)R * (unsigned long long)L);
         }
@@ -295,7 +300,7 @@ __global__ void __launch_bounds__(THREADS, 512 / THREADS) k1_score_kernel(const 
                     o.score_f = rc ? nb : sc; o.score_r = rc ? sc : nb;   // the loser's entry is only ever compared
                     o.col_f = rc ? 0 : col; o.col_r = rc ? col : 0;
                     out[t] = o;
-                    mix.sstate[t] = (int32_t)(((uint32_t)nb << 16) | (uint32_t)(rc << 1) | 1u);
+                    mix.sstate[t] = (int32_t)(((uint32_t)nb << 16) | (uint32_t)(rc << 1) | 1u | (sc < K1_WEAK ? 4u : 0u));
                 }
                 else
                 {
@@ -324,7 +329,8 @@ __global__ void mix_plan_kernel(const int32_t *__restrict__ pair_task, int64_t n
     if (t1 < 0) return;
     if (win_done[task_win[t1]]) return;
     const int R1 = read_len[task_read[t1]], R2 = t2 >= 0 ? read_len[task_read[t2]] : 0;
-    if (t2 >= 0 && (sstate[t1] & 1) && (sstate[t2] & 1))
+    const int s1 = sstate[t1], s2 = t2 >= 0 ? sstate[t2] : 0;
+    if (t2 >= 0 && (s1 & 1) && (s2 & 1) && !((s1 | s2) & 4))
     {
         const int cls = (R1 > 152 || R2 > 152);
         const int at = atomicAdd(cnt + 2 + cls, 1);

@@ -128,15 +128,75 @@ __global__ void plan_kernel(const int32_t *__restrict__ task_read, const int32_t
 
 // After the scans: does the round fit its arenas? (E_end / TE_end: totals of the exclusive scans)
 __global__ void fit_kernel(const int64_t *__restrict__ E_end, const int64_t *__restrict__ TE_end,
-                           const int32_t *__restrict__ cls_count, RoundCtl *__restrict__ ctl, int round, int64_t cap_units,
+                           int32_t *__restrict__ cls_count, RoundCtl *__restrict__ ctl, int round, int64_t cap_units,
                            int64_t cap_words)
 {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     const int64_t nu = *E_end, nw = *TE_end;
     ctl->need_units = nu; ctl->need_words = nw; ctl->round = round;
-    for (int c = 0; c < TC_N; ++c) ctl->cls[c] = cls_count[c];
+    for (int c = 0; c < TC_N; ++c) { ctl->cls[c] = cls_count[c]; cls_count[c] = 0; }
     ctl->active = 0; ctl->live_pairs = 0;
     ctl->ovf = (nu > cap_units || nw > cap_words) ? 1 : 0;
+}
+
+// Both exclusive scans of a round (record units -> E, trace words -> TE; n1 = tasks + 1 entries each) and the fit check in
+// ONE single-block launch, for batches of up to SCAN2_MAX tasks: at that size the two library scans are four launches of
+// a few microseconds each, i.e. mostly launch latency on the round's critical path. Also re-arms the class counters.
+constexpr int SCAN2_THREADS = 1024, SCAN2_MAX = 128 * 1024;
+__global__ void __launch_bounds__(SCAN2_THREADS) scan2_fit_kernel(const int64_t *__restrict__ units, int64_t *__restrict__ E,
+                                                               const int64_t *__restrict__ tunits, int64_t *__restrict__ TE, int n1,
+                                                               int32_t *__restrict__ cls_count, RoundCtl *__restrict__ ctl, int round,
+                                                               int64_t cap_units, int64_t cap_words)
+{
+    // warp w owns the contiguous chunk [w * per, (w + 1) * per) (per: a multiple of 32); lanes read consecutive
+    // entries, so every access is coalesced. Entry n1 - 1 only receives the totals: its own value is never read.
+    __shared__ long long sh[2][SCAN2_THREADS / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n = n1 - 1;
+    const int per = ((n1 + SCAN2_THREADS - 1) / SCAN2_THREADS) * 32;
+    const int lo = min(n1, warp * per), hi = min(n1, lo + per);
+    long long a = 0, b = 0;
+    for (int i = lo + lane; i < hi; i += 32) if (i < n) { a += units[i]; b += tunits[i]; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { a += __shfl_xor_sync(0xffffffffu, a, o); b += __shfl_xor_sync(0xffffffffu, b, o); }
+    if (lane == 0) { sh[0][warp] = a; sh[1][warp] = b; }
+    __syncthreads();
+    if (warp == 0)
+    {
+        // exclusive prefix over the 32 warp totals; lane 31 also keeps the grand totals
+        const long long wa = sh[0][lane], wb = sh[1][lane];
+        long long pa = wa, pb = wb;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1)
+        {
+            const long long xa = __shfl_up_sync(0xffffffffu, pa, o), xb = __shfl_up_sync(0xffffffffu, pb, o);
+            if (lane >= o) { pa += xa; pb += xb; }
+        }
+        sh[0][lane] = pa - wa; sh[1][lane] = pb - wb;
+        if (lane == 31)
+        {
+            ctl->need_units = pa; ctl->need_words = pb; ctl->round = round;
+            for (int c = 0; c < TC_N; ++c) { ctl->cls[c] = cls_count[c]; cls_count[c] = 0; }
+            ctl->active = 0; ctl->live_pairs = 0;
+            ctl->ovf = (pa > cap_units || pb > cap_words) ? 1 : 0;
+        }
+    }
+    __syncthreads();
+    long long ca = sh[0][warp], cb = sh[1][warp];     // running exclusive prefix of this warp's chunk
+    for (int base = lo; base < hi; base += 32)
+    {
+        const int i = base + lane;
+        const long long u = (i < n && i < hi) ? units[i] : 0, w = (i < n && i < hi) ? tunits[i] : 0;
+        long long pu = u, pw = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1)
+        {
+            const long long xu = __shfl_up_sync(0xffffffffu, pu, o), xw = __shfl_up_sync(0xffffffffu, pw, o);
+            if (lane >= o) { pu += xu; pw += xw; }
+        }
+        if (i < hi) { E[i] = ca + pu - u; TE[i] = cb + pw - w; }
+        ca += __shfl_sync(0xffffffffu, pu, 31); cb += __shfl_sync(0xffffffffu, pw, 31);
+    }
 }
 
 template <int RPL>

@@ -1,21 +1,24 @@
 // sviper_b200/host/shim/sviper/polishing.h -- the drop-in seam, without touching a line of the reference.
 //
 // The reference's sviper.h does `#include <sviper/polishing.h>` (include/sviper/sviper.h:14). Putting THIS directory in
-// front of the reference's include path makes the unmodified src/sviper.cpp pick up this file instead. It pulls in the
+// front of the reference's include path makes the reference's sources pick up this file instead. It pulls in the
 // reference's own polishing.h (compute_baseQ_stats etc. stay the reference's code) and replaces exactly the two calls of
 // the hot path (SURVEY 8b seams 1 and 2):
 //
 //   sviper::polish_to_perfection(reads1, reads2, ref, config)        polishing.h:319-346, called at sviper.h:431
-//       -> one variant submitted to the device batch scheduler (sviper_b200::BatchScheduler): the OpenMP threads of
-//          src/sviper.cpp:43-47 keep running polish_variant's I/O half, whatever they have submitted at the same time
-//          is polished as one device batch (svp_polish_batch), the caller blocks on its own future (seam 3)
+//       -> one variant submitted to the asynchronous device scheduler (Gateway::polish -> svp_submit_polish). With the
+//          reference part attached (see the basics.h shim) the final alignment runs in the same device job. The caller is
+//          suspended (a fiber of the prepare / device / finish pipeline, pipeline.hpp) or blocks (a plain OpenMP thread
+//          of the unmodified src/sviper.cpp) until its result is back (seam 3).
 //   seqan::globalAlignment(gapsRef, gapsSeq, Score<double>, AlignConfig<0,0,0,0>, ConvexGaps)   sviper.h:457-460
-//       -> svp_final_align_batch; the device CIGAR is written back into the two Gaps objects, so the reference's own
-//          getCigarString (sviper.h:466) and everything behind it run unchanged
+//       -> the CIGAR the device job already produced (or svp_final_align_batch when called on other sequences) is written
+//          back into the two Gaps objects, so the reference's own getCigarString (sviper.h:466) and everything behind it
+//          run unchanged
 //
-// Build (sviper_b200/csrc/Makefile, target ../host/sviper_b200_cli):
-//   g++ -std=c++14 -O3 -DNDEBUG -fopenmp -I sviper_b200/host/shim -I $REF/extern/seqan/include -I $REF/include \
-//       $REF/src/sviper.cpp -lsviper_b200 -lz
+// Two programs are built from this (sviper_b200/csrc/Makefile):
+//   sviper_b200        host/sviper_b200_main.cpp: the reference's main() sequence with the OpenMP loop replaced by the
+//                      fiber pipeline -- prepare threads never wait for the device
+//   sviper_b200_cli    the reference's UNMODIFIED src/sviper.cpp: each OpenMP thread blocks on its own variant
 // GPUs: SVIPER_B200_DEVICES="0,1,2,3" (default "0"). There is no CPU fallback: without a GPU the first call throws.
 #pragma once
 
@@ -27,47 +30,14 @@
 #include <mutex>
 
 #include <seqan/align.h>
+#include <seqan/seq_io.h>
 
-#include "../../polisher.hpp"
+#include <sviper/basics.h>   // (the shim in this directory: VariantScope, append_ref_flanks hook)
 
 namespace sviper_b200
 {
 namespace shim
 {
-inline std::vector<int> devices()
-{
-    std::vector<int> d;
-    char const * e = std::getenv("SVIPER_B200_DEVICES");
-    std::string s = e ? e : "0";
-    size_t p = 0;
-    while (p < s.size())
-    {
-        size_t q = s.find(',', p);
-        if (q == std::string::npos) q = s.size();
-        if (q > p) d.push_back(std::atoi(s.substr(p, q - p).c_str()));
-        p = q + 1;
-    }
-    if (d.empty()) d.push_back(0);
-    return d;
-}
-
-inline BatchScheduler & scheduler()
-{
-    // SVIPER_B200_LINGER_US (default 500): how long a device worker waits for further OpenMP threads to arrive
-    char const * e = std::getenv("SVIPER_B200_LINGER_US");
-    static BatchScheduler s(devices(), 256, e ? (unsigned)std::atoi(e) : 500u);
-    return s;
-}
-
-// final alignments are single jobs of a millisecond: one context behind a mutex
-inline std::vector<CigarElement> final_alignment(std::string const & ref_part, std::string const & polished, double * score)
-{
-    static Polisher p(devices()[0]);
-    static std::mutex m;
-    std::lock_guard<std::mutex> lk(m);
-    return p.final_alignment(ref_part, polished, score);
-}
-
 template <typename TString>
 inline std::string to_std_string(TString const & s)
 {
@@ -105,20 +75,50 @@ inline seqan::Dna5String polish_to_perfection(seqan::StringSet<seqan::Dna5QStrin
     cfg.stdev_insert_size = config.stdev_insert_size_of_short_reads;
     cfg.ref_flank_length = (int)config.ref_flank_length;
     cfg.min_coverage = config.min_coverage;
-    std::unique_ptr<b200::PackedVariant> pv(new b200::PackedVariant(b200::shim::to_qreads(reads1), b200::shim::to_qreads(reads2),
-                                                                   b200::shim::to_std_string(ref), cfg));
-    std::unique_ptr<b200::ResultBuffers> rb = b200::shim::scheduler().submit(std::move(pv)).get();
-    if (rb->res.status != SVP_OK) throw std::runtime_error("sviper_b200: polish_to_perfection failed on the device");
+    // the reference part of the final alignment: the readRegion call of sviper.h:447-450, same expressions and types
+    // (int - unsigned is unsigned arithmetic there), made here so that the final alignment rides in the same device job
+    b200::shim::VariantScope & vs = b200::shim::scope();
+    std::string ref_part;
+    bool with_final = false;
+    if (vs.have_region && vs.flank == config.ref_flank_length)
+    {
+        seqan::Dna5String rp;
+        seqan::readRegion(rp, *vs.fai, vs.fai_idx, std::max(1u, vs.start - config.ref_flank_length),
+                          std::min(vs.end + config.ref_flank_length, static_cast<unsigned>(vs.ref_length)));
+        ref_part = b200::shim::to_std_string(rp);
+        with_final = !ref_part.empty();
+    }
+    vs.have_region = false; vs.have_final = false;
+    b200::PackedVariant pv(b200::shim::to_qreads(reads1), b200::shim::to_qreads(reads2), b200::shim::to_std_string(ref), cfg,
+                           with_final ? &ref_part : nullptr);
+    b200::ResultBuffers rb(seqan::length(ref), (int)(seqan::length(ref) + ref_part.size() + 4096));
+    b200::Gateway::instance().polish(pv, rb);   // suspends this fiber / blocks this thread until the device batch is done
+    if (rb.res.status == SVP_ERR_UNSUPPORTED || rb.res.status == SVP_ERR_ARG || rb.res.status == SVP_ERR_CAPACITY)
+    {
+        // outside the device's per-variant limits (include/sviper_b200.h; e.g. a read longer than SVP_MAX_READ_LEN): the
+        // other variants are not affected, this one stays unpolished -- said loudly, never silently replaced by CPU code
+        std::cerr << "[sviper_b200] variant not polished: input outside the device limits (status " << rb.res.status
+                  << "); its consensus is left as built from the long reads" << std::endl;
+        config.fix_indels = true;
+        return ref;
+    }
+    if (rb.res.status != SVP_OK) throw std::runtime_error("sviper_b200: polish_to_perfection failed on the device");
     // the side effects of polishing.h:319-346 on config (config.h:72-90)
-    config.rounds += rb->res.rounds;
-    config.substituted_bases += rb->res.substituted_bases;
-    config.inserted_bases += rb->res.inserted_bases;
-    config.deleted_bases += rb->res.deleted_bases;
-    config.mappQ_mean = rb->res.mappQ_mean;
+    config.rounds += rb.res.rounds;
+    config.substituted_bases += rb.res.substituted_bases;
+    config.inserted_bases += rb.res.inserted_bases;
+    config.deleted_bases += rb.res.deleted_bases;
+    config.mappQ_mean = rb.res.mappQ_mean;
     config.alpha = config.mappQ_mean / config.baseQ_mean;
     config.fix_indels = true;
-    config.cov_profile.assign(rb->cov.begin(), rb->cov.begin() + rb->res.cov_len);
-    seqan::Dna5String out = rb->sequence();
+    config.cov_profile.assign(rb.cov.begin(), rb.cov.begin() + rb.res.cov_len);
+    std::string polished = rb.sequence();
+    if (with_final)
+    {
+        vs.have_final = true; vs.ref_part.swap(ref_part); vs.polished = polished; vs.cigar = rb.cigar();
+        vs.score = rb.res.final_score;
+    }
+    seqan::Dna5String out = polished;
     return out;
 }
 }  // namespace sviper
@@ -134,8 +134,16 @@ inline double globalAlignment(Gaps<Dna5String, ArrayGaps> & gapsRef, Gaps<Dna5St
         scoreGapOpen(scoring) != -100000)                                     // config.h:66-69: what the device kernel implements
         throw std::logic_error("sviper_b200: final alignment called with other scores than SViperConfig's");
     double score = 0;
-    std::vector<sviper_b200::CigarElement> cigar = sviper_b200::shim::final_alignment(
-        sviper_b200::shim::to_std_string(source(gapsRef)), sviper_b200::shim::to_std_string(source(gapsSeq)), &score);
+    std::vector<sviper_b200::CigarElement> cigar;
+    sviper_b200::shim::VariantScope & vs = sviper_b200::shim::scope();
+    std::string const h = sviper_b200::shim::to_std_string(source(gapsRef)), v = sviper_b200::shim::to_std_string(source(gapsSeq));
+    if (vs.have_final && h == vs.ref_part && v == vs.polished)
+    {
+        cigar.swap(vs.cigar); score = vs.score;      // computed in the variant's polish job
+        vs.have_final = false;
+    }
+    else
+        cigar = sviper_b200::Gateway::instance().final_alignment(h, v, &score);
     clearGaps(gapsRef); clearGaps(gapsSeq);
     clearClipping(gapsRef); clearClipping(gapsSeq);
     size_t view = 0;                                                          // position in the gapped rows

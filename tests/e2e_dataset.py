@@ -36,64 +36,96 @@ def cigar_str(ops):
     return "".join(out)
 
 
-def make(outdir, seed=1, contig_len=60000, cov_short=30, cov_long=20, k=400, only_filter_paths=False):
-    rng = np.random.default_rng(seed)
-    os.makedirs(outdir, exist_ok=True)
-    ref = rng.integers(0, 4, contig_len).astype(np.uint8)
-    # (type, 0-based ref position of the first affected base / insertion point, length)
-    lens = [100, 300, 300, 100, 800, 800]
-    svs = [("DEL" if i % 2 == 0 else "INS", 6000 + 7000 * i, lens[i % 6]) for i in range(max(0, (contig_len - 18000) // 7000))]
-    svs.append(("DEL", contig_len - 8000, 200))          # supported by long reads, but (almost) no short reads there: FAIL4
-    # ---- the sample's haplotype, with for every alt base the reference coordinate it maps to -----------------
+def haplotype(ref, svs, ins_seqs):
+    """the sample's sequence with, for every base, the reference coordinate it maps to and whether it is an inserted base"""
     alt, amap, akind = [], [], []          # akind: 0 = reference base, 1 = inserted base
     p = 0
-    for typ, pos, ln in svs:
+    for typ, pos, ln in sorted(svs, key=lambda x: x[1]):
         alt.append(ref[p:pos]); amap.append(np.arange(p, pos)); akind.append(np.zeros(pos - p, np.uint8))
         if typ == "DEL":
             p = pos + ln
         else:
-            alt.append(rng.integers(0, 4, ln).astype(np.uint8)); amap.append(np.full(ln, pos)); akind.append(np.ones(ln, np.uint8))
+            alt.append(ins_seqs[pos]); amap.append(np.full(ln, pos)); akind.append(np.ones(ln, np.uint8))
             p = pos
-    alt.append(ref[p:]); amap.append(np.arange(p, contig_len)); akind.append(np.zeros(contig_len - p, np.uint8))
-    alt = np.concatenate(alt); amap = np.concatenate(amap); akind = np.concatenate(akind)
+    alt.append(ref[p:]); amap.append(np.arange(p, len(ref))); akind.append(np.zeros(len(ref) - p, np.uint8))
+    return np.concatenate(alt), np.concatenate(amap), np.concatenate(akind)
+
+
+def make(outdir, seed=1, contig_len=60000, cov_short=30, cov_long=20, k=400, only_filter_paths=False, extras=True):
+    """extras: records beyond the plain DEL / INS calls: an insertion of 1.2 kb; a deletion only the long reads
+    carry (the short reads polish it away: FAIL5 in refine_variant, sviper.h:474-479); calls on contigs the short-read /
+    long-read BAM does not know (FAIL6 / FAIL7, sviper.h:189-211); a call whose best supporting long read is too short to crop
+    (the silent `return false` of sviper.h:327: FILTER and QUAL stay as they came in). FAIL3 (sviper.h:337-348) cannot be
+    reached: the crop loop either appends a sequence or returns at :327 on its first element."""
+    rng = np.random.default_rng(seed)
+    os.makedirs(outdir, exist_ok=True)
+    ref = rng.integers(0, 4, contig_len).astype(np.uint8)
+    # (type, 0-based ref position of the first affected base / insertion point, length)
+    lens = [100, 300, 300, 100, 800, 1200 if extras else 800]
+    svs = [("DEL" if i % 2 == 0 else "INS", 6000 + 7000 * i, lens[i % 6]) for i in range(max(0, (contig_len - 18000) // 7000))]
+    svs.append(("DEL", contig_len - 8000, 200))          # supported by long reads, but (almost) no short reads there: FAIL4
+    ins_seqs = {pos: rng.integers(0, 4, ln).astype(np.uint8) for typ, pos, ln in svs if typ == "INS"}
+    # a 45 bp insertion that only the long-read haplotype carries: every short read across it votes "gap", the indel
+    # rounds delete it again and refine_variant no longer finds the call in the final alignment
+    phantom = ("INS", 9500, 45) if (extras and len(svs) > 2 and not only_filter_paths) else None
+    if phantom:
+        ins_seqs[phantom[1]] = rng.integers(0, 4, phantom[2]).astype(np.uint8)
+    alt, amap, akind = haplotype(ref, svs, ins_seqs)                                        # what the short reads sample
+    alt_l, amap_l, akind_l = haplotype(ref, svs + ([phantom] if phantom else []), ins_seqs)  # what the long reads sample
 
     # ---- FASTA + .fai -----------------------------------------------------------------------------------------
     fa = os.path.join(outdir, "ref.fa")
-    with open(fa, "w") as f:
-        f.write(">chr1\n")
-        seq = s(ref)
-        for i in range(0, len(seq), 60):
-            f.write(seq[i:i + 60] + "\n")
-    with open(fa + ".fai", "w") as f:
-        f.write("chr1\t%d\t6\t60\t61\n" % contig_len)
+    small = {nm: rng.integers(0, 4, 3000).astype(np.uint8) for nm in ("chrA", "chrB")} if extras else {}
+    with open(fa, "w") as f, open(fa + ".fai", "w") as fi:
+        off = 0
+        for nm, sq in [("chr1", ref)] + sorted(small.items()):
+            hdr = ">%s\n" % nm
+            f.write(hdr); off += len(hdr)
+            seq = s(sq)
+            fi.write("%s\t%d\t%d\t60\t61\n" % (nm, len(seq), off))
+            for i in range(0, len(seq), 60):
+                f.write(seq[i:i + 60] + "\n"); off += len(seq[i:i + 60]) + 1
+    long_refs = [("chr1", contig_len)]
+    short_refs = [("chr1", contig_len)] + ([("chrB", 3000)] if extras else [])
 
     # ---- long reads: 8-15 kb of the haplotype, 10% errors, true CIGAR against the reference ------------------
     # no long read reaches into the last 3.5 kb (FAIL1 record there)
     recs = []
-    n_long = int(cov_long * len(alt) / 11500)
-    for i in range(n_long):
+    n_long = int(cov_long * len(alt_l) / 11500)
+    crop_victim = svs[2] if (extras and len(svs) > 3 and not only_filter_paths) else None
+    for i in range(n_long + (1 if crop_victim else 0)):
         ln = int(rng.integers(8000, 15001))
-        st = int(rng.integers(0, max(1, len(alt) - 3500 - ln)))
+        st = int(rng.integers(0, max(1, len(alt_l) - 3500 - ln)))
+        mapq = int(rng.integers(20, 61))
+        if i == n_long:
+            # the read with the best mapping quality at this call carries a further 450-base insertion 150 bp behind the
+            # deletion: its crop is more than k bases longer than expected, and polish_variant returns at sviper.h:327
+            # without touching the record
+            a0 = int(np.searchsorted(amap_l, crop_victim[1] - 2000)); ln = 4500; st = a0; mapq = 70
+            junk_at = crop_victim[1] + crop_victim[2] + 150
         ops, opref, bases = [], [], []          # opref: reference coordinate of an M / D op (None for I)
         prev_ref = None
         u_all = rng.random(ln); nb_all = rng.integers(0, 4, (ln, 2))
-        for j, a in enumerate(range(st, min(len(alt), st + ln))):
-            r = int(amap[a])
-            if akind[a] == 0 and prev_ref is not None and r > prev_ref + 1:
+        for j, a in enumerate(range(st, min(len(alt_l), st + ln))):
+            r = int(amap_l[a])
+            if akind_l[a] == 0 and prev_ref is not None and r > prev_ref + 1:
                 ops.extend("D" * (r - prev_ref - 1)); opref.extend(range(prev_ref + 1, r))     # the deletion as one element
-            if akind[a] == 1:
-                ops.append("I"); opref.append(None); bases.append(alt[a])
+            if i == n_long and crop_victim and akind_l[a] == 0 and r == junk_at:
+                for x in rng.integers(0, 4, 450):
+                    ops.append("I"); opref.append(None); bases.append(x)
+            if akind_l[a] == 1:
+                ops.append("I"); opref.append(None); bases.append(alt_l[a])
                 continue
             u = u_all[j]
             if u < 0.03:
-                ops.append("M"); opref.append(r); bases.append((alt[a] + 1 + nb_all[j, 0] % 3) % 4)
+                ops.append("M"); opref.append(r); bases.append((alt_l[a] + 1 + nb_all[j, 0] % 3) % 4)
             elif u < 0.065:
-                ops.append("M"); opref.append(r); bases.append(alt[a])
+                ops.append("M"); opref.append(r); bases.append(alt_l[a])
                 ops.append("I"); opref.append(None); bases.append(nb_all[j, 1])
             elif u < 0.10:
                 ops.append("D"); opref.append(r)
             else:
-                ops.append("M"); opref.append(r); bases.append(alt[a])
+                ops.append("M"); opref.append(r); bases.append(alt_l[a])
             prev_ref = r
         while ops and ops[0] != "M":                                       # an alignment starts and ends on a match
             if ops[0] == "I":
@@ -104,10 +136,10 @@ def make(outdir, seed=1, contig_len=60000, cov_short=30, cov_long=20, k=400, onl
                 bases.pop()
             ops.pop(); opref.pop()
         first_ref = opref[0]
-        recs.append(("long%04d" % i, 16 if rng.random() < 0.5 else 0, 0, first_ref, int(rng.integers(20, 61)),
+        recs.append(("long%04d" % i, 16 if rng.random() < 0.5 else 0, 0, first_ref, mapq,
                      cigar_str(ops), -1, -1, 0, s(np.array(bases, np.uint8)), "*"))
     recs.sort(key=lambda x: x[3])
-    bamwriter.write_bam(os.path.join(outdir, "long.bam"), [("chr1", contig_len)], recs)
+    bamwriter.write_bam(os.path.join(outdir, "long.bam"), long_refs, recs)
 
     # ---- short reads: fragments of the haplotype, both mates placed at their reference coordinate -----------
     recs = []
@@ -131,12 +163,19 @@ def make(outdir, seed=1, contig_len=60000, cov_short=30, cov_long=20, k=400, onl
         recs.append((name, fa_, 0, pa, 60, "150M", 0, pb, fl, s(a), qa))
         recs.append((name, fb_, 0, pb, 60, "150M", 0, pa, -fl, s(b), qb))
     recs.sort(key=lambda x: x[3])
-    bamwriter.write_bam(os.path.join(outdir, "short.bam"), [("chr1", contig_len)], recs)
+    bamwriter.write_bam(os.path.join(outdir, "short.bam"), short_refs, recs)
 
     # ---- candidate VCF: jittered calls + the FILTER paths -------------------------------------------------------
     vcf = os.path.join(outdir, "candidates.vcf")
     with open(vcf, "w") as f:
         f.write("##fileformat=VCFv4.2\n##contig=<ID=chr1,length=%d>\n" % contig_len)
+        extra_calls = []
+        if phantom:
+            extra_calls.append("chr1\t%d\tsvP\tN\t<INS>\t.\tPASS\tSVTYPE=INS;END=%d;SVLEN=%d\tGT\t0/1\n" %
+                               (phantom[1] + 2, phantom[1] + 2, phantom[2]))                                # FAIL5 candidate
+        if extras:
+            extra_calls.append("chrA\t1000\tsvA\tN\t<DEL>\t.\tPASS\tSVTYPE=DEL;END=1200;SVLEN=-200\tGT\t0/1\n")   # FAIL6
+            extra_calls.append("chrB\t1000\tsvB\tN\t<DEL>\t.\tPASS\tSVTYPE=DEL;END=1200;SVLEN=-200\tGT\t0/1\n")   # FAIL7
         f.write('##INFO=<ID=SVTYPE,Number=1,Type=String,Description="Type">\n')
         f.write('##INFO=<ID=END,Number=1,Type=Integer,Description="End">\n')
         f.write('##INFO=<ID=SVLEN,Number=1,Type=Integer,Description="Length">\n')
@@ -154,6 +193,8 @@ def make(outdir, seed=1, contig_len=60000, cov_short=30, cov_long=20, k=400, onl
         f.write("chr1\t%d\tsv%d\tN\t<DEL>\t.\tPASS\tSVTYPE=DEL;END=%d;SVLEN=-200\tGT\t0/1\n" % (contig_len - 12000, n, contig_len - 11800)); n += 1   # FAIL2
         f.write("chr1\t%d\tsv%d\tN\t<DEL>\t.\tPASS\tSVTYPE=DEL;END=%d;SVLEN=-200\tGT\t0/1\n" % (contig_len - 2000, n, contig_len - 1800)); n += 1   # FAIL1
         f.write("chr2\t1000\tsv%d\tN\t<DEL>\t.\tPASS\tSVTYPE=DEL;END=1200;SVLEN=-200\tGT\t0/1\n" % n); n += 1         # FAIL0
+        for line in extra_calls:
+            f.write(line); n += 1
     return dict(ref=fa, vcf=vcf, long=os.path.join(outdir, "long.bam"), short=os.path.join(outdir, "short.bam"), k=k,
                 n_records=n, n_sv=0 if only_filter_paths else len(svs) - 1)
 

@@ -259,6 +259,7 @@ def test_mixed_strand_rounds_are_exact_and_save_cells(ctx, config1_batch):
         plain = api.Context(0)
     finally:
         del os.environ["SVP_NO_MIXED"]
+    plain.polish_batch(config1_batch, with_final=True)      # sizes the per-round arenas (a round that does not fit is repeated)
     plain.k1_cells(reset=1)
     res0 = plain.polish_batch(config1_batch, with_final=True)
     cells0 = plain.k1_cells(reset=1)

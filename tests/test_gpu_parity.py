@@ -282,8 +282,8 @@ def test_async_scheduler(ctx):
 
 
 def test_round_loop_variants_agree(ctx, monkeypatch):
-    """The round loop queues round r + 1 before it has seen the outcome of round r, and sizes the per-round arenas from an
-    estimate. Neither may change a result: (a) SVP_SYNC_ROUNDS=1 waits for every round; (b) SVP_SMALL_ARENAS=1 starts from
+    """The round loop sizes the per-round arenas from an
+    estimate. Neither may change a result: (a) SVP_SPECULATIVE_ROUNDS=1 queues round r + 1 before round r's outcome is known; (b) SVP_SMALL_ARENAS=1 starts from
     arenas that are far too small, so the first round of every batch overflows, leaves the state untouched and is repeated
     after the arenas have grown (RoundCtl::ovf); (c) 64- and 128-thread blocks of the score kernel."""
     from sviper_b200 import api
@@ -297,11 +297,14 @@ def test_round_loop_variants_agree(ctx, monkeypatch):
             assert np.array_equal(g["polished"], w["polished"]) and g["cigar"] == w["cigar"] and g["rounds"] == w["rounds"]
             assert np.array_equal(g["cov"], w["cov"]) and (g["subst"], g["ins"], g["dele"]) == (w["subst"], w["ins"], w["dele"])
 
-    monkeypatch.setenv("SVP_SYNC_ROUNDS", "1")
+    monkeypatch.setenv("SVP_SPECULATIVE_ROUNDS", "1")
     c = api.Context(0)
     same(c.polish_batch(vs, with_final=True))
+    monkeypatch.setenv("SVP_SMALL_ARENAS", "1")
+    same(c.polish_batch(vs, with_final=True))
+    monkeypatch.delenv("SVP_SMALL_ARENAS")
     c.close()
-    monkeypatch.delenv("SVP_SYNC_ROUNDS")
+    monkeypatch.delenv("SVP_SPECULATIVE_ROUNDS")
     for lanes in (1, 2):
         c = api.Context(0)
         c.set_lanes(lanes)
