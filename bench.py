@@ -218,30 +218,28 @@ LANES_NOTE = ("the batch runs as 4 concurrent parts on the GPU (library default,
               "the roofline are taken in a separate single-part pass of the same steps")
 
 
-def pin_to_gpu_numa_node(local):
-    """Keeps this rank's host threads (and the library's lane threads, which inherit the mask) on the cores NVML
-    reports as local to the rank's GPU: the round loop waits on the device a dozen times per step, and every one of
-    those round trips is slower from the far socket."""
-    try:
-        import pynvml
-        pynvml.nvmlInit()
-        h = pynvml.nvmlDeviceGetHandleByIndex(local)
-        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
-        cpus = [64 * i + b for i, w in enumerate(words) for b in range(64) if (w >> b) & 1]
-        cpus = [c for c in cpus if c in os.sched_getaffinity(0)]
-        if cpus:
-            os.sched_setaffinity(0, cpus)
-        return len(cpus)
-    except Exception:
-        return 0
-
-
 def run_gpu(args):
     import torch
+    import bench_configs as bc
     from sviper_b200 import api
+    # synthetic inputs of the other configs come from forked worker processes: before this process touches CUDA / NCCL
+    env_rank, env_world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    single_extras = env_world == 1 and not args.quick
+    cores_per_rank = max(1, host_cores() // max(1, env_world))
+    t0 = time.perf_counter()
+    n_c3 = 0 if args.quick else args.c3_variants
+    c3_shard = bc.generate(bc.c3_variant, range(env_rank, n_c3, env_world), min(8, cores_per_rank)) if n_c3 else []
+    c3_gen = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    c4_list = bc.generate(bc.c4_variant, range(args.c4_variants), min(8, cores_per_rank)) if (single_extras and args.c4_variants) else []
+    c4_gen = time.perf_counter() - t0
     rank, world, local = dist_setup(args.gpus)
     torch.cuda.set_device(local)
-    pinned_cpus = pin_to_gpu_numa_node(local) if world > 1 else 0
+    gloo = None
+    if world > 1:
+        import torch.distributed as dist
+        gloo = dist.new_group(backend="gloo")
+    pinned_cpus = bc.pin_rank_to_core_slice(local, world) if world > 1 else 0
     stream = torch.cuda.current_stream().cuda_stream          # the library launches on torch's current stream
     ctx = api.Context(local, stream)
     # weak scaling with EXACTLY fixed per-GPU work: every rank polishes its own copy of the same batch (nothing is shared
@@ -472,7 +470,22 @@ def run_gpu(args):
             dt, used, _ = cpu_port_run(sample); kind = "port"
         out["cpu_baseline"] = {"value": len(sample) / dt, "unit": "variants/s", "cores": used, "kind": kind,
                                "sample": "%d variants of the same batch, one per host thread, %.1f s" % (len(sample), dt)}
+    # ---- the other named configs (extra keys; each bounded so that the default run stays within a few minutes) ----
+    if n_c3:
+        c3 = bc.run_sharded_c3(ctx, rank, world, flush, gloo, n_c3, c3_shard, c3_gen, barrier, max_over_ranks, sum_over_ranks)
+        if out is not None:
+            out["sharded_candidate_list"] = c3
+        del c3_shard
+    if single_extras and out is not None:
+        peak_gcups = out["roofline"]["peak"]
+        if c4_list:
+            out["large_insertions"] = bc.run_c4(ctx, flush, c4_list, c4_gen, host_cores())
+            del c4_list
+        if args.c5_full:
+            out["alignment_microbench_full"] = bc.run_c5_full(ctx, flush, make_c5_tasks, host_cores(), peak_gcups)
     ctx.close()
+    if single_extras and out is not None and args.whole_program_records:
+        out["whole_program"] = bc.run_whole_program(args.whole_program_records, host_cores(), local)
     if world > 1:
         import torch.distributed as dist
         dist.barrier(); dist.destroy_process_group()
@@ -521,6 +534,12 @@ def main():
     ap.add_argument("--seed", type=int, default=1000, help="seed of the synthetic batch")
     ap.add_argument("--distinct-shards", action="store_true", help="rank r polishes the batch of seed + r")
     ap.add_argument("--variants", type=int, default=100, help="variants per GPU per step (configs[1]: 100)")
+    ap.add_argument("--quick", action="store_true", help="configs[1] only: skip the extra keys for the other configs")
+    ap.add_argument("--c3-variants", type=int, default=5000, help="configs[2]: records of the sharded candidate list (0: skip)")
+    ap.add_argument("--c4-variants", type=int, default=200, help="configs[3]: large insertions, N = 1 only (0: skip)")
+    ap.add_argument("--no-c5-full", dest="c5_full", action="store_false", help="skip configs[4] at full size (N = 1 only)")
+    ap.add_argument("--whole-program-records", type=int, default=32,
+                    help="reference binary vs pipeline program on files, N = 1 only (0: skip)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -110,7 +110,9 @@ public:
                     }
                 }
                 if (inflight == 0) break;
-                // 3. nothing to prepare (or the in-flight cap is reached): wait for one of this thread's variants
+                // 3. nothing to prepare (or the in-flight cap is reached): whatever is queued on the devices must run now,
+                // then wait for one of this thread's variants
+                if (on_idle_) on_idle_();
                 std::unique_lock<std::mutex> lk(s.m);
                 waits_.fetch_add(1);
                 s.cv.wait(lk, [&] { return !s.ready.empty(); });
@@ -130,6 +132,8 @@ public:
         s.cv.notify_one();
     }
 
+    // called by a thread right before it blocks for lack of work (the Gateway hooks svp_flush in here)
+    void set_on_idle(std::function<void()> f) { on_idle_ = std::move(f); }
     int threads() const { return T_; }
     size_t peak_inflight() const { return peak_.load(); }
     size_t thread_waits() const { return waits_.load(); }
@@ -154,6 +158,7 @@ private:
     }
 
     int T_, cap_;
+    std::function<void()> on_idle_;
     std::vector<Slot> slots_;
     std::atomic<size_t> next_{0}, started_{0}, peak_{0}, waits_{0};
 };
@@ -223,6 +228,8 @@ public:
         return s;
     }
     size_t n_gpus() const { return dev_.size(); }
+    // start on whatever is queued now (a lane otherwise waits for SVP_BATCH_TARGET variants or for the linger time)
+    void flush() { for (auto & d : dev_) svp_flush(d->ctx); }
 
     ~Gateway()
     {

@@ -52,6 +52,7 @@ int main(int argc, char const ** argv)
         char const * e = std::getenv("SVIPER_B200_INFLIGHT");
         sviper_b200::Gateway::instance();   // fail before any work if there is no usable GPU
         sviper_b200::Pipeline pipe((int)info.cmd_options.threads, e && std::atoi(e) > 0 ? std::atoi(e) : 64);
+        pipe.set_on_idle([] { sviper_b200::Gateway::instance().flush(); });
         pipe.run(variants.size(), [&](size_t vidx) { polish_variant(variants[vidx], info); });
         if (std::getenv("SVIPER_B200_STATS"))
         {

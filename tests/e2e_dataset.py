@@ -51,7 +51,7 @@ def haplotype(ref, svs, ins_seqs):
     return np.concatenate(alt), np.concatenate(amap), np.concatenate(akind)
 
 
-def make(outdir, seed=1, contig_len=60000, cov_short=30, cov_long=20, k=400, only_filter_paths=False, extras=True):
+def make(outdir, seed=1, contig_len=60000, cov_short=30, cov_long=20, k=400, only_filter_paths=False, extras=True, calls=None):
     """extras: records beyond the plain DEL / INS calls: an insertion of 1.2 kb; a deletion only the long reads
     carry (the short reads polish it away: FAIL5 in refine_variant, sviper.h:474-479); calls on contigs the short-read /
     long-read BAM does not know (FAIL6 / FAIL7, sviper.h:189-211); a call whose best supporting long read is too short to crop
@@ -63,6 +63,8 @@ def make(outdir, seed=1, contig_len=60000, cov_short=30, cov_long=20, k=400, onl
     # (type, 0-based ref position of the first affected base / insertion point, length)
     lens = [100, 300, 300, 100, 800, 1200 if extras else 800]
     svs = [("DEL" if i % 2 == 0 else "INS", 6000 + 7000 * i, lens[i % 6]) for i in range(max(0, (contig_len - 18000) // 7000))]
+    if calls is not None:
+        svs = list(calls)                                # (make_c2: a given list of calls instead of the C1 mix)
     svs.append(("DEL", contig_len - 8000, 200))          # supported by long reads, but (almost) no short reads there: FAIL4
     ins_seqs = {pos: rng.integers(0, 4, ln).astype(np.uint8) for typ, pos, ln in svs if typ == "INS"}
     # a 45 bp insertion that only the long-read haplotype carries: every short read across it votes "gap", the indel
@@ -197,6 +199,17 @@ def make(outdir, seed=1, contig_len=60000, cov_short=30, cov_long=20, k=400, onl
             f.write(line); n += 1
     return dict(ref=fa, vcf=vcf, long=os.path.join(outdir, "long.bam"), short=os.path.join(outdir, "short.bam"), k=k,
                 n_records=n, n_sv=0 if only_filter_paths else len(svs) - 1)
+
+
+def make_c2(outdir, n_records=100, seed=2):
+    """BASELINE.json configs[1] / SURVEY 8d C2 as FILES: n_records DELs with lengths log-uniform in 50..1000 bp, 7 kb apart on
+    one contig, 30x 2x150 bp short reads, 20x long reads at 10% error, -k 400 (plus the FILTER-path records of make())."""
+    rng = np.random.default_rng(seed * 7919)
+    calls = [("DEL", 6000 + 7000 * i, int(round(np.exp(rng.uniform(np.log(50), np.log(1000)))))) for i in range(n_records)]
+    contig_len = 6000 + 7000 * n_records + 18000
+    d = make(outdir, seed=seed, contig_len=contig_len, extras=False, calls=calls)
+    d["contig_len"] = contig_len
+    return d
 
 
 if __name__ == "__main__":

@@ -47,17 +47,22 @@ def test_cpp_host_matches_reference_fixture():
     assert n == 64
 
 
-def test_gpu_build_of_reference_program_routes_the_hot_path_to_the_library():
-    """sviper_b200_cli = the reference's unmodified src/sviper.cpp compiled with host/shim in front of its include path:
-    its only imports from the library are the two hot-path entry points, and SeqAn's convex-gap DP (the final alignment
-    of sviper.h:457-460) is not instantiated any more, i.e. the overload in the shim was chosen."""
-    cli = os.path.join(HOST, "sviper_b200_cli")
-    if not os.path.exists(cli):
-        pytest.skip("sviper_b200_cli not built (needs the reference tree at build time)")
-    syms = subprocess.check_output(["nm", "-C", cli], text=True)
-    imports = sorted(set(line.split()[-1] for line in syms.split("\n") if " U svp_" in line))
-    assert "svp_polish_batch" in imports and "svp_final_align_batch" in imports
-    assert "onvex" not in syms
+def test_gpu_programs_route_the_hot_path_to_the_library():
+    """sviper_b200_cli = the reference's unmodified src/sviper.cpp, sviper_b200 = the pipeline program; both compiled from
+    the reference's sources with host/shim in front of the include path and linked with --gc-sections. Their imports from
+    the library are the asynchronous scheduler and the stand-alone final alignment; the reference's CPU polishing loop
+    (renamed away by the shim) and SeqAn's convex-gap DP (sviper.h:457-460) are not part of the programs: nothing refers
+    to them, i.e. the shim's overloads were chosen and there is no CPU hot path to fall back to."""
     ref = os.path.join(ROOT, "oracle", "_ref", "sviper")
+    for name in ("sviper_b200_cli", "sviper_b200"):
+        exe = os.path.join(HOST, name)
+        if not os.path.exists(exe):
+            pytest.skip("%s not built (needs the reference tree at build time)" % name)
+        syms = subprocess.check_output(["nm", "-C", exe], text=True)
+        imports = sorted(set(line.split()[-1] for line in syms.split("\n") if " U svp_" in line))
+        assert {"svp_submit_polish", "svp_wait_any", "svp_final_align_batch"} <= set(imports), imports
+        assert "polish_to_perfection_reference_cpu" not in syms
+        assert "onvex" not in syms
     if os.path.exists(ref):
-        assert "onvex" in subprocess.check_output(["nm", "-C", ref], text=True)     # the reference does instantiate it
+        rs = subprocess.check_output(["nm", "-C", ref], text=True)
+        assert "onvex" in rs and "polish_to_perfection" in rs          # the reference does instantiate both
