@@ -162,6 +162,30 @@ typedef struct
 
 int svp_final_align_batch(svp_ctx *ctx, int32_t n, const svp_final_in *in, svp_result *out);
 
+/* Final alignment of ONE pair without any allocation -- NO COUNTERPART IN THE REFERENCE; added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it). Same kernels and results as svp_final_align_batch, but all scratch (tables, padded sequence copies, job
+ * descriptor, band rows, trace) lives in one file-scope device array of fixed size (about 10.7 MB, held by every GPU that
+ * loads the library until the process exits), so ref_part_len and seq_len are limited to SVP_STATIC_MAX_LEN: longer
+ * sequences are refused with SVP_ERR_CAPACITY (svp_last_error names the limit). Unlike the rest of this header the sequence,
+ * CIGAR and result pointers are DEVICE memory owned by the caller (bases uint8 0..4; cigar buffers of cigar_cap elements).
+ * The call only queues three kernels on the context's stream and returns; it calls no cudaMalloc / cudaFree / cudaHostAlloc
+ * and no allocating library routine. The first call on a device does a one-time synchronous set-up (symbol address, 64 KB of
+ * tables copied into the scratch): make it outside a graph capture. Every call on a device shares the scratch, which keeps
+ * the previous call's contents (what must start at zero is cleared by the call itself): calls that overlap on the GPU --
+ * different streams or contexts -- race; calls on one stream are ordered and safe. result->n_cigar > cigar_cap means the
+ * CIGAR was truncated (result->stored elements were written). */
+#define SVP_STATIC_MAX_LEN 4096
+typedef struct
+{
+    int32_t n_cigar;     /* CIGAR elements of the alignment */
+    int32_t stored;      /* elements written to cigar_op_dev / cigar_cnt_dev (<= cigar_cap) */
+    double score;        /* the alignment score the reference discards (sviper.h:457) */
+} svp_final_static_result;
+int svp_final_align_static(svp_ctx *ctx, const uint8_t *ref_part_dev, int32_t ref_part_len, const uint8_t *seq_dev,
+                           int32_t seq_len, char *cigar_op_dev, uint32_t *cigar_cnt_dev, int32_t cigar_cap,
+                           svp_final_static_result *result_dev);
+
 /* include/sviper/evaluate_final_mapping.h:17-28 (host arithmetic, provided for completeness) */
 double svp_assign_quality(int32_t n_cigar, int32_t flanking_region);
 

@@ -71,7 +71,7 @@ EXPORTS = ["svp_create", "svp_destroy", "svp_last_error", "svp_version", "svp_al
            "svp_debug_round", "svp_probe_dpx", "svp_stats", "svp_set_lanes", "svp_refine_variant", "svp_refine_info",
            "svp_format_quality", "svp_record_supports_variant", "svp_read_region_boundaries",
            "svp_alignment_length_in_ref", "svp_cut_down_high_coverage", "svp_merge_record_group", "svp_k1_cells",
-           "svp_flush", "svp_probe_fp64", "svp_engine_config", "svp_engine_stats", "svp_window_capacity"]
+           "svp_flush", "svp_final_align_static", "svp_probe_fp64", "svp_engine_config", "svp_engine_stats", "svp_window_capacity"]
 
 _lib = None
 
@@ -103,6 +103,8 @@ def lib():
         L.svp_submit_polish.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(WindowIn), C.POINTER(Result)]
         L.svp_wait_any.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.POINTER(Result))]
         L.svp_flush.argtypes = [C.c_void_p]
+        L.svp_final_align_static.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
+                                             C.c_int32, C.c_void_p]
         L.svp_engine_config.argtypes = [C.c_void_p, C.c_int32, C.c_int32]
         L.svp_engine_stats.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         L.svp_window_capacity.restype = C.c_int32

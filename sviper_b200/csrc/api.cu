@@ -364,3 +364,148 @@ double svp_assign_quality(int32_t n_cigar, int32_t flanking_region)
 }
 
 }  // extern "C"
+
+// =====================================================================================================================
+// svp_final_align_static: the final alignment (K5 + traceback) for callers that must not allocate (CUDA graph capture,
+// tight serving loops, harnesses that forbid cudaMalloc). No counterpart in the reference.
+// Same kernels as svp_final_align_batch, but every byte of scratch -- gap-step / edge tables, padded
+// copies of the two sequences, the job descriptor, the band boundary rows and the 4-bit trace -- lives in ONE file-scope
+// device array of fixed size, and inputs / outputs are DEVICE pointers of the caller. The entry point calls no
+// cudaMalloc / cudaFree / cudaHostAlloc and no allocating library routine; everything is queued on the context's stream.
+// =====================================================================================================================
+namespace svp_static
+{
+constexpr int MAXD = SVP_STATIC_MAX_LEN;                       // longest sequence on either side
+constexpr int NBANDS = (MAXD + svp::K5_BAND - 1) / svp::K5_BAND;
+constexpr size_t al(size_t x) { return (x + 255) & ~(size_t)255; }
+constexpr int TBL = MAXD + 4;                                  // table entries 0..TBL
+constexpr size_t OFF_GAPSTEP = 0;
+constexpr size_t OFF_EDGE = OFF_GAPSTEP + al((size_t)(TBL + 1) * 8);
+constexpr size_t OFF_REF = OFF_EDGE + al((size_t)(TBL + 1) * 8);
+constexpr size_t OFF_SEQ = OFF_REF + al((size_t)MAXD + 64);
+constexpr size_t OFF_JOB = OFF_SEQ + al((size_t)MAXD + 64);
+constexpr size_t OFF_END = OFF_JOB + al(sizeof(svp::FinalJob));
+constexpr size_t OFF_BNDS = OFF_END + al(sizeof(svp::FinalEnd));
+constexpr size_t OFF_BNDV = OFF_BNDS + al((size_t)(MAXD + 8) * 8);
+constexpr size_t OFF_BNDVL = OFF_BNDV + al((size_t)(MAXD + 8) * 8);
+constexpr size_t OFF_TRACE = OFF_BNDVL + al((size_t)(MAXD + 8) * 4);
+constexpr size_t TRACE_BYTES = (size_t)((MAXD + 1) / 2 + svp::K5_THREADS) * (size_t)(NBANDS * svp::K5_THREADS) * 4;
+constexpr size_t TOTAL = OFF_TRACE + al(TRACE_BYTES);          // ~10.7 MB for MAXD = 4096
+}  // namespace svp_static
+
+// Held by every GPU that loads the library until the process exits. Shared by all calls and all contexts of a device:
+// two calls that overlap on the GPU (different streams) race on it.
+static __device__ __align__(256) unsigned char svp_static_scratch[svp_static::TOTAL];
+
+namespace svp_static
+{
+// Copies the caller's sequences into the scratch (bases beyond N -> N, zero padding behind the end: the kernel reads one
+// column past it), writes the job descriptor and clears what must start at zero (the end-cell record; the caller's result).
+// Device code names the array directly.
+__global__ void prepare_kernel(const uint8_t *__restrict__ ref, int n, const uint8_t *__restrict__ seq, int m,
+                               svp::CigarOut *__restrict__ result)
+{
+    uint8_t *sref = svp_static_scratch + OFF_REF, *sseq = svp_static_scratch + OFF_SEQ;
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x, nt = gridDim.x * blockDim.x;
+    for (int i = tid; i < n + 16; i += nt) { uint8_t b = i < n ? ref[i] : 0; sref[i] = b > 4 ? 4 : b; }
+    for (int i = tid; i < m + 16; i += nt) { uint8_t b = i < m ? seq[i] : 0; sseq[i] = b > 4 ? 4 : b; }
+    if (tid == 0)
+    {
+        svp::FinalJob j;
+        j.ref = sref; j.seq = sseq; j.n = n; j.m = m;
+        int nb = (m + svp::K5_BAND - 1) / svp::K5_BAND; if (nb < 1) nb = 1;
+        j.row_threads = nb * svp::K5_THREADS;
+        j.trace_off = 0; j.bnd_off = 0; j.valid = 1;
+        *reinterpret_cast<svp::FinalJob *>(svp_static_scratch + OFF_JOB) = j;
+        svp::FinalEnd e; e.S = 0; e.H = 0; e.V = 0;
+        *reinterpret_cast<svp::FinalEnd *>(svp_static_scratch + OFF_END) = e;
+        svp::CigarOut o; o.n_cigar = 0; o.stored = 0; o.score = 0;
+        *result = o;
+    }
+}
+
+// per device: address of the scratch array as the DEVICE sees it (the symbol itself is only a host-side stand-in),
+// and whether the tables have been uploaded
+struct PerDevice { unsigned char *base = nullptr; bool ready = false; };
+static PerDevice g_dev[64];
+static std::mutex g_mu;
+}  // namespace svp_static
+
+// Set-up, once per device, with that device current: the device address of the scratch array (cudaGetSymbolAddress -- in
+// host code the array's name is NOT a device address) and the two tables every job shares, computed with the same IEEE
+// operations as ensure_tables() (api_final.inc) into static host arrays and copied into the scratch. No allocation.
+static int svp_static_setup(svp_ctx *ctx, unsigned char **base_out)
+{
+    using namespace svp_static;
+    if (ctx->device < 0 || ctx->device >= 64) return svp_fail_msg(ctx, SVP_ERR_ARG, "svp_final_align_static: device index beyond 63");
+    std::lock_guard<std::mutex> lk(g_mu);
+    PerDevice &pd = g_dev[ctx->device];
+    if (!pd.ready)
+    {
+        CK(cudaSetDevice(ctx->device));
+        unsigned char *p = nullptr;
+        CK(cudaGetSymbolAddress((void **)&p, svp_static_scratch));
+        if (!p) return svp_fail_msg(ctx, SVP_ERR_CUDA, "svp_final_align_static: no device address for the scratch array");
+        static double gs[TBL + 1], ed[TBL + 1];
+        gs[0] = 0;
+        for (int len = 1; len <= TBL; ++len)
+        {
+            volatile double q = F_GO / (double)len;
+            gs[len] = (q < F_GE) ? (double)q : F_GE;
+        }
+        ed[0] = 0;
+        volatile double V = F_INF, S = 0;
+        int vl = 1;
+        for (int i = 1; i <= TBL; ++i)
+        {
+            volatile double ext = V + gs[vl];
+            volatile double opn = S + F_GO;
+            if (ext < opn) { V = opn; vl = 1; } else { V = ext; vl = vl + 1; }
+            S = V;
+            ed[i] = S;
+        }
+        CK(cudaMemcpy(p + OFF_GAPSTEP, gs, sizeof gs, cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(p + OFF_EDGE, ed, sizeof ed, cudaMemcpyHostToDevice));
+        pd.base = p; pd.ready = true;
+    }
+    *base_out = pd.base;
+    return SVP_OK;
+}
+
+extern "C" int svp_final_align_static(svp_ctx *ctx, const uint8_t *ref_part_dev, int32_t ref_part_len, const uint8_t *seq_dev,
+                                      int32_t seq_len, char *cigar_op_dev, uint32_t *cigar_cnt_dev, int32_t cigar_cap,
+                                      svp_final_static_result *result_dev)
+{
+    using namespace svp_static;
+    static_assert(sizeof(svp_final_static_result) == sizeof(svp::CigarOut), "result layout");
+    if (!ctx) return SVP_ERR_ARG;
+    if (!ref_part_dev || !seq_dev || !cigar_op_dev || !cigar_cnt_dev || !result_dev || cigar_cap < 1)
+        return svp_fail_msg(ctx, SVP_ERR_ARG, "svp_final_align_static: null pointer or empty CIGAR buffer");
+    if (ref_part_len < 1 || seq_len < 1) return svp_fail_msg(ctx, SVP_ERR_ARG, "svp_final_align_static: empty sequence");
+    if (ref_part_len > MAXD || seq_len > MAXD)
+        return svp_fail_msg(ctx, SVP_ERR_CAPACITY, "svp_final_align_static: sequence longer than SVP_STATIC_MAX_LEN (" +
+                                                       std::to_string(MAXD) + "); use svp_final_align_batch");
+    unsigned char *base = nullptr;
+    int rc = svp_static_setup(ctx, &base);
+    if (rc) return rc;
+    CK(cudaSetDevice(ctx->device));
+    svp::CigarOut *result = reinterpret_cast<svp::CigarOut *>(result_dev);
+    prepare_kernel<<<8, 256, 0, ctx->stream>>>(ref_part_dev, ref_part_len, seq_dev, seq_len, result);
+    CK(cudaGetLastError());
+    svp::K5Tables tb;
+    tb.gapstep = reinterpret_cast<const double *>(base + OFF_GAPSTEP);
+    tb.edge = reinterpret_cast<const double *>(base + OFF_EDGE);
+    tb.size = TBL;
+    const svp::FinalJob *job = reinterpret_cast<const svp::FinalJob *>(base + OFF_JOB);
+    svp::FinalEnd *ends = reinterpret_cast<svp::FinalEnd *>(base + OFF_END);
+    uint32_t *trace = reinterpret_cast<uint32_t *>(base + OFF_TRACE);
+    svp::k5_final_kernel<true><<<1, svp::K5_THREADS, (size_t)(TBL + 1) * 8, ctx->stream>>>(
+        job, tb, F_MM, F_MX, F_GO, F_INF, trace, reinterpret_cast<double *>(base + OFF_BNDS),
+        reinterpret_cast<double *>(base + OFF_BNDV), reinterpret_cast<int32_t *>(base + OFF_BNDVL), ends);
+    CK(cudaGetLastError());
+    svp::k5_traceback_kernel<<<1, svp::K5TB_WARPS * 32, 0, ctx->stream>>>(job, 1, trace, ends, F_INF, cigar_op_dev, cigar_cnt_dev,
+                                                                        cigar_cap, result);
+    CK(cudaGetLastError());
+    ctx->n_launches += 3;
+    return SVP_OK;
+}
