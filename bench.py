@@ -538,7 +538,7 @@ def main():
     ap.add_argument("--c3-variants", type=int, default=5000, help="configs[2]: records of the sharded candidate list (0: skip)")
     ap.add_argument("--c4-variants", type=int, default=200, help="configs[3]: large insertions, N = 1 only (0: skip)")
     ap.add_argument("--no-c5-full", dest="c5_full", action="store_false", help="skip configs[4] at full size (N = 1 only)")
-    ap.add_argument("--whole-program-records", type=int, default=32,
+    ap.add_argument("--whole-program-records", type=int, default=100,
                     help="reference binary vs pipeline program on files, N = 1 only (0: skip)")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -106,7 +106,9 @@ orc_round *orc_polish_round(orc_config *c, int np,
     orc_insprof *ins = (orc_insprof *)calloc((size_t)L + 1, sizeof *ins);
     int i, p, Lp, pos;
     R->np = np; R->mobs = (orc_mob *)calloc((size_t)np + 1, sizeof(orc_mob));
-    /* mapping.h:148-179 */
+    /* mapping.h:148-179. The pairs are independent (each writes its own mob), so large windows (configs[3]: 13 kb x 1,300
+     * pairs) are spread over the host cores; nested inside orc_polish_many's loop over variants this stays sequential. */
+#pragma omp parallel for schedule(dynamic, 4) if (np >= 64 && L >= 3000)
     for (i = 0; i < np; ++i)
     {
         orc_mob *mb = &R->mobs[i];

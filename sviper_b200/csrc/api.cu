@@ -10,6 +10,7 @@
 #include <condition_variable>
 #include <deque>
 #include <cub/device/device_scan.cuh>
+#include <nvtx3/nvToolsExt.h>
 #include "ctx.cuh"
 #include "k1_score.cuh"
 
@@ -111,6 +112,7 @@ static svp_ctx *make_ctx(int cuda_device, void *cuda_stream, bool is_lane)
     for (int i = 0; i < 2; ++i) cudaEventCreateWithFlags(&ctx->ev_ctl[i], cudaEventDisableTiming);
     if (const char *sr = getenv("SVP_SPECULATIVE_ROUNDS")) ctx->sync_rounds = atoi(sr) != 1;
     if (const char *kt = getenv("SVP_K1_THREADS")) ctx->k1_threads = atoi(kt);
+    if (const char *kg = getenv("SVP_K5_GLOBAL_TABLE")) ctx->k5_global_table = atoi(kg) == 1;
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) ctx->arena_budget = (size_t)(free_b * 0.6);
     const char *fw = getenv("SVP_FULL_WINDOW");

@@ -147,6 +147,7 @@ struct svp_ctx
     // ---- final alignment ----
     DevBuf fjobs, fref, fseq, ftrace, fbndS, fbndV, fbndVL, fends, fcig_op, fcig_cnt, fcig_out, gapstep, edge;
     int table_size = 0;
+    bool k5_global_table = false;           // SVP_K5_GLOBAL_TABLE=1: K5 reads the gap-step table from global memory at every size (test switch)
     // ---- host staging / result gather ----
     HostStage stage;
     DevBuf win_done, gather_desc, gather_out;

@@ -190,3 +190,27 @@ def check_case(c, e):
         check_round(c["v"], c["fix"], e)
     else:
         check_polish(c["v"], e)
+
+
+def oracle_full(v):
+    """polish_to_perfection + final alignment of one variant through the oracle (ctypes releases the GIL: callers run
+    several of these on a thread pool). Returns what the parity tests compare."""
+    r1p, r2p = packed(v)
+    cfg = oracle_cfg(v, r1p, r2p)
+    seq, cov = orc.polish_to_perfection(cfg, *r1p, *r2p, v["consensus"])
+    sc, ops = orc.align_convex(v["ref_part"], seq)
+    return dict(polished=seq, cov=cov, counters=(cfg.rounds, cfg.subst, cfg.ins, cfg.del_), final_score=sc, cigar=orc.cigar(ops))
+
+
+def assert_matches_oracle(vs, got, workers=None):
+    """every variant of a GPU result list against the oracle, bit for bit; the oracle runs on all host cores"""
+    import concurrent.futures as cf
+    import numpy as np
+    with cf.ThreadPoolExecutor(max_workers=workers or min(len(vs), os.cpu_count() or 1)) as ex:
+        want = list(ex.map(oracle_full, vs))
+    for i, (w, g) in enumerate(zip(want, got)):
+        assert np.array_equal(w["polished"], g["polished"]), "variant %d: polished sequence" % i
+        assert np.array_equal(w["cov"], g["cov"]), "variant %d: coverage profile" % i
+        assert w["counters"] == (g["rounds"], g["subst"], g["ins"], g["dele"]), "variant %d: counters" % i
+        assert w["final_score"] == g["final_score"] and w["cigar"] == g["cigar"], "variant %d: final alignment" % i
+    return want

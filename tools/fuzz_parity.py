@@ -2,7 +2,12 @@
 """Randomised parity sweep on a GPU box: small variants of widely varying shape (read lengths 20..256, coverage,
 flank, error rates, N bases, insert windows, garbage / same-strand / mate-less pairs), polished in batches through
 the C ABI and compared with the oracle's literal restatement of polish_to_perfection + the convex final
-alignment. Bit-exact or it prints the offending seed and exits 1.   usage: tools/fuzz_parity.py [seconds] [seed0]"""
+alignment. Bit-exact or it prints the offending seed and exits 1.
+usage: tools/fuzz_parity.py [seconds] [seed0] [report.json]
+The report (written also when a mismatch stops the campaign) holds the seed range -- random_variant(seed) regenerates any
+case -- the batch sizes, per-shape counts of what was covered, and the offending seed if there was one."""
+import collections
+import json
 import sys
 import time
 
@@ -12,6 +17,9 @@ sys.path.insert(0, ".")
 from tests import refcases as rc  # noqa: E402
 
 orc, synth = rc.orc, rc.synth
+
+
+SHAPES = collections.Counter()
 
 
 def random_variant(seed):
@@ -38,7 +46,17 @@ def random_variant(seed):
         v["ref_part"] = np.concatenate([t[:cut], rng.integers(0, 4, int(rng.integers(1, 80))).astype(np.uint8), t[cut:]])
     else:
         v["ref_part"] = np.concatenate([t[:cut], t[min(len(t) - flank, cut + int(rng.integers(1, 40))):]])
+    SHAPES["read_len=%d" % read_len] += 1
+    SHAPES["cons_err=%g" % err] += 1
+    SHAPES["insert=%g+-%g" % (ins_mean, ins_sd)] += 1
+    SHAPES["with_N" if any((r == 4).any() for r in v["reads1"]) else "no_N"] += 1
+    SHAPES["dummy_mate" if any(len(r) == 0 for r in v["reads2"]) else "all_mated"] += 1
+    SHAPES["ref_part_ins" if len(v["ref_part"]) > len(t) else "ref_part_del"] += 1
+    SHAPES["window<=200" if len(v["consensus"]) <= 200 else ("window<=400" if len(v["consensus"]) <= 400 else "window>400")] += 1
     return v
+
+
+OUTCOMES = collections.Counter()
 
 
 def check(ctx, vs, seeds):
@@ -53,25 +71,40 @@ def check(ctx, vs, seeds):
         if ok:
             sc, ops = orc.align_convex(v["ref_part"], seq)
             ok = sc == g["final_score"] and orc.cigar(ops) == g.get("cigar", [])
+        OUTCOMES["rounds=%d" % g["rounds"]] += 1
+        OUTCOMES["realigned_rounds=%d" % g["alignment_rounds"]] += 1
+        OUTCOMES["cigar_elements<=3" if g["n_cigar"] <= 3 else "cigar_elements>3"] += 1
+        OUTCOMES["edited" if (g["subst"] + g["ins"] + g["dele"]) else "unchanged"] += 1
         if not ok:
             print("MISMATCH at seed", sd)
-            return False
-    return True
+            return sd
+    return None
 
 
 def main():
     from sviper_b200 import api
     budget = float(sys.argv[1]) if len(sys.argv) > 1 else 120.0
     seed = int(sys.argv[2]) if len(sys.argv) > 2 else 100000
+    report = sys.argv[3] if len(sys.argv) > 3 else None
     ctx = api.Context(0)
-    t0, n = time.time(), 0
-    while time.time() - t0 < budget:
+    t0, n, seed0, batches, bad = time.time(), 0, seed, collections.Counter(), None
+    while time.time() - t0 < budget and bad is None:
         k = int(np.random.default_rng(seed).integers(1, 40))          # batch sizes on both sides of the lane split
         seeds = list(range(seed, seed + k))
         vs = [random_variant(s) for s in seeds]
-        if not check(ctx, vs, seeds):
-            sys.exit(1)
+        bad = check(ctx, vs, seeds)
+        batches["batch<8" if k < 8 else ("batch<16" if k < 16 else "batch>=16")] += 1
         seed += k; n += k
+    if report:
+        with open(report, "w") as f:
+            json.dump({"tool": "tools/fuzz_parity.py", "seconds": time.time() - t0, "variants": n, "first_seed": seed0,
+                       "last_seed": seed - 1, "regenerate": "tools/fuzz_parity.py: random_variant(seed)",
+                       "mismatch_at_seed": bad, "batches": dict(sorted(batches.items())),
+                       "shapes": dict(sorted(SHAPES.items())), "outcomes": dict(sorted(OUTCOMES.items())),
+                       "compared": "polished sequence, coverage profile, rounds / subst / ins / del counters, mappQ_mean, "
+                                   "final fp64 score (==) and CIGAR against the oracle, bit for bit"}, f, indent=1)
+    if bad is not None:
+        sys.exit(1)
     print("fuzz_parity: %d variants, all bit-exact (%.0f s)" % (n, time.time() - t0))
 
 
