@@ -278,6 +278,44 @@ int svp_merge_record_group(int32_t n, const svp_bam_record *recs, int32_t *chose
                            int32_t *seq_len);
 
 /* ------------------------------------------------------------------------------------------------
+ * The pairwise DP fills of build_consensus (include/sviper/basics.h:484-520 ->
+ * seqan::globalMsaAlignment, extern/seqan/include/seqan/graph_msa/graph_align_tcoffee_msa.h:323-548). ~90 % of
+ * build_consensus is spent filling pairwise DP matrices for the T-Coffee library; these entry points do the fills on the
+ * device and return the TRACE MATRICES in SeqAn's own byte layouts, so that the host side hands them to SeqAn's unchanged
+ * traceback code and everything after it (alignment graph, guide tree, progressive alignment, column vote) stays the
+ * reference's host code. One session = one globalMsaAlignment call on one context.
+ *   svp_msa_begin        the sequence pairs selectPairs() chose (graph_align_tcoffee_msa.h:346-347): h = str[0] = matrix
+ *                        columns, v = str[1] = rows; scores = SimpleScore(match, mismatch, gap_extend, gap_open) (5,-3,-1,-3
+ *                        at basics.h:494)
+ *   svp_msa_global_fill  global pairwise library (graph_msa/graph_align_tcoffee_library.h:979-1008 -> globalAlignment(...,
+ *                        Gotoh()), align/global_alignment_unbanded.h:386-407): trace_out[i] receives the (n + 1) x (m + 1)
+ *                        TraceBitMap_ bytes of DPMatrix_<.., FullDPMatrix>, element (row i, column j) at j * (m + 1) + i
+ *                        (align/dp_formula_affine.h:66-125, :243-325), res[i].S/H/V the bottom-right cell
+ *   svp_msa_local_fill   one round of the local pairwise library's clumping Smith-Waterman (library.h:252-390
+ *                        _alignSmithWaterman): trace_out[i] receives n * ((m + 1) / 2) bytes (two rows per byte, odd rows in
+ *                        the high nibble), res[i] score / row / col / dir = score_max, indexPair, initialDir.
+ *                        new_forbidden[i] = n_new[i] (col, row) pairs (1-based) the caller's traceback of the round before
+ *                        marked with _setForbiddenCell; they stay forbidden for the rest of the session.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct
+{
+    const uint8_t *h; int32_t n;     /* bases 0..4 */
+    const uint8_t *v; int32_t m;
+} svp_msa_pair;
+
+typedef struct
+{
+    int32_t score, row, col, dir;
+    int32_t S, H, V;
+} svp_msa_fill_result;
+
+int svp_msa_begin(svp_ctx *ctx, int32_t n_pairs, const svp_msa_pair *pairs, int32_t match, int32_t mismatch,
+                  int32_t gap_extend, int32_t gap_open);
+int svp_msa_global_fill(svp_ctx *ctx, int32_t n, const int32_t *pair_idx, uint8_t *const *trace_out, svp_msa_fill_result *res);
+int svp_msa_local_fill(svp_ctx *ctx, int32_t n, const int32_t *pair_idx, const int32_t *const *new_forbidden,
+                       const int32_t *n_new, uint8_t *const *trace_out, svp_msa_fill_result *res);
+
+/* ------------------------------------------------------------------------------------------------
  * Asynchronous device batch scheduler (replaces the loop body at src/sviper.cpp:43-47; SURVEY 8b "submissions
  * asynchronous with an explicit wait"). svp_submit_polish queues one variant and returns at once; one worker thread per
  * lane (svp_set_lanes) forms device batches from what is queued, runs them (staging, H2D, every round, final alignment,

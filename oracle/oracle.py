@@ -37,6 +37,10 @@ def lib():
             build()
         L = C.CDLL(path)
         L.orc_align_semiglobal.restype = C.c_int
+        L.orc_msa_sw_fill.restype = None
+        L.orc_msa_sw_fill.argtypes = [u8p, C.c_int, u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, u8p, u8p, C.POINTER(C.c_int)]
+        L.orc_msa_global_fill.restype = C.c_int
+        L.orc_msa_global_fill.argtypes = [u8p, C.c_int, u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, u8p, C.POINTER(C.c_int)]
         L.orc_align_convex.restype = C.c_double
         L.orc_align_convex.argtypes = [u8p, C.c_int, u8p, C.c_int, C.c_double, C.c_double, C.c_double, C.c_double,
                                        C.c_char_p, i32p]
@@ -187,6 +191,43 @@ def align_convex(ref_part, polished, MM=90000.0, MX=-80000.0, GE=-1.0, GO=-10000
     nops = C.c_int()
     s = lib().orc_align_convex(_p(a), len(a), _p(b), len(b), MM, MX, GE, GO, ops, C.byref(nops))
     return s, ops.raw[:nops.value].decode()
+
+
+MSA_SCORES = (5, -3, -1, -3)   # match, mismatch, gap extend, gap open: SimpleScore(5, -3, -1, -3), basics.h:494
+
+
+def fnv1a(buf):
+    """64-bit FNV-1a of a byte buffer (what ref_harness prints for a trace matrix)"""
+    h = 1469598103934665603
+    for b in bytes(buf):
+        h = ((h ^ b) * 1099511628211) & 0xFFFFFFFFFFFFFFFF
+    return h
+
+
+def msa_sw_fill(h, v, forbidden_cells=(), scores=MSA_SCORES):
+    """_alignSmithWaterman (graph_align_tcoffee_library.h:252-390). forbidden_cells: (col, row), 1-based.
+    Returns (trace bytes, score_max, row, col, initialDir)."""
+    a = np.ascontiguousarray(h, np.uint8); b = np.ascontiguousarray(v, np.uint8)
+    n, m = len(a), len(b)
+    forb = None
+    if len(forbidden_cells):
+        forb = np.zeros(n * m, np.uint8)
+        for col, row in forbidden_cells:
+            forb[(col - 1) * m + (row - 1)] = 1
+    trace = np.zeros(n * ((m + 1) // 2) + 1, np.uint8)
+    out = (C.c_int * 4)()
+    lib().orc_msa_sw_fill(_p(a), n, _p(b), m, *scores, _p(forb) if forb is not None else None, _p(trace), out)
+    return trace[:n * ((m + 1) // 2)], out[0], out[1], out[2], out[3]
+
+
+def msa_global_fill(h, v, scores=MSA_SCORES):
+    """trace matrix of the global pairwise library's Gotoh alignment. Returns (trace bytes (n+1)*(m+1), score, (S, H, V))"""
+    a = np.ascontiguousarray(h, np.uint8); b = np.ascontiguousarray(v, np.uint8)
+    n, m = len(a), len(b)
+    trace = np.zeros((n + 1) * (m + 1), np.uint8)
+    end = (C.c_int * 3)()
+    sc = lib().orc_msa_global_fill(_p(a), n, _p(b), m, *scores, _p(trace), end)
+    return trace, sc, (end[0], end[1], end[2])
 
 
 def cigar(ops):

@@ -4,6 +4,7 @@
 #include "oracle_polish.c"
 #include "oracle_final.c"
 #include "oracle_eval.c"
+#include "oracle_msa.c"
 #ifdef _OPENMP
 #include <omp.h>
 #endif

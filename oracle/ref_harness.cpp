@@ -18,6 +18,11 @@
 //   SUPPORT type pos svlen begin cigar         record_supports_variant on a long-read record (variant.h:239-275)
 //   REGION  begin cigar ref_begin ref_end      get_read_region_boundaries (basics.h:189-241)
 //   CUTCOV  cov n  then n lines "name begin mapq cigar"   cut_down_high_coverage (basics.h:403-442)
+//   MSA     n  then n lines "seq mapq"       sviper::build_consensus (basics.h:484-520: globalMsaAlignment + column vote)
+//   SWFILL  a b k  then k pairs "col row"    seqan::_alignSmithWaterman (graph_msa/graph_align_tcoffee_library.h:252-390): the
+//                                          legacy clumping Smith-Waterman fill of the local pairwise library, forbidden cells given
+//   GFILL   a b                            the trace matrix of globalAlignment(String<Fragment>, ..., Gotoh()) as the global pairwise
+//                                          library computes it (global_alignment_unbanded.h:386-407 -> dp_algorithm_impl.h:1393-1469)
 //   MERGE   n  then n lines "name flag rid begin mapq cigar seq" (sorted by name)   merge_alignments
 //                                                  (merge_split_alignments.h:378-561, called at sviper.h:266)
 #include <thread>
@@ -32,6 +37,7 @@
 
 #include <seqan/align.h>
 #include <seqan/bam_io.h>
+#include <seqan/graph_msa.h>
 #include <sviper/config.h>
 #include <sviper/polishing.h>
 #include <sviper/basics.h>
@@ -55,6 +61,13 @@ static std::string row(TGaps const & g)
     for (unsigned i = 0; i < length(g); ++i)
         s += isGap(g, i) ? '-' : (char)Dna5(g[i]);
     return s.empty() ? "*" : s;
+}
+
+static unsigned long long fnv1a(unsigned char const * p, size_t n)
+{
+    unsigned long long h = 1469598103934665603ull;
+    for (size_t i = 0; i < n; ++i) { h ^= p[i]; h *= 1099511628211ull; }
+    return h;
 }
 
 static Dna5QString mkread(std::string const & s, std::string const & q)
@@ -258,6 +271,82 @@ int main(int argc, char ** argv)
             sviper::cut_down_high_coverage(recs, (int16_t)cov);
             std::cout << "CUTCOV n=" << recs.size() << " keep=";
             for (size_t i = 0; i < recs.size(); ++i) std::cout << (i ? "," : "") << recs[i].qName;
+            std::cout << "\n";
+        }
+        else if (cmd == "MSA")
+        {
+            unsigned n; in >> n;
+            StringSet<Dna5String> seqs;
+            std::vector<double> quals;
+            for (unsigned i = 0; i < n; ++i)
+            {
+                std::string sq; double q; in >> sq >> q;
+                appendValue(seqs, Dna5String(sq)); quals.push_back(q);
+            }
+            Dna5String cns = sviper::build_consensus(seqs, quals);
+            std::cout << "MSA len=" << length(cns) << " seq=" << (length(cns) ? dna(cns) : std::string("*")) << "\n";
+        }
+        else if (cmd == "SWFILL")
+        {
+            std::string a, b; unsigned k; in >> a >> b >> k;
+            Dna5String s0 = a, s1 = b;
+            StringSet<Dna5String, Dependent<> > str;
+            appendValue(str, s0); appendValue(str, s1);
+            String<bool> forbidden;
+            resize(forbidden, length(s0) * length(s1), false);
+            for (unsigned i = 0; i < k; ++i) { size_t col, row; in >> col >> row; forbidden[(col - 1) * length(s1) + (row - 1)] = true; }
+            String<unsigned char> trace;
+            unsigned char initialDir;
+            size_t indexPair[2];
+            int sc = _alignSmithWaterman(trace, str, Score<int, Simple>(5, -3, -1, -3), initialDir, indexPair, forbidden);
+            std::cout << "SWFILL score=" << sc << " row=" << indexPair[0] << " col=" << indexPair[1] << " dir=" << (int)initialDir
+                      << " tracelen=" << length(trace) << " hash=" << fnv1a(begin(trace, Standard()), length(trace)) << "\n";
+        }
+        else if (cmd == "GFILL")
+        {
+            std::string a, b; in >> a >> b;
+            Dna5String seqH = a, seqV = b;
+            Score<int, Simple> sc(5, -3, -1, -3);
+            // the set-up of _computeAlignment (dp_algorithm_impl.h:1393-1469) with the fill and the traceback as separate steps
+            typedef DPCell_<int, AffineGaps> TCell;
+            typedef TraceBitMap_<>::Type TTraceValue;
+            typedef SetupAlignmentProfile_<DPGlobal, FreeEndGaps_<False, False, False, False>, AffineGaps,
+                                           TracebackOn<TracebackConfig_<SingleTrace, GapsLeft> > >::Type TDPProfile;
+            typedef DPContext<TCell, TTraceValue> TContext;
+            TContext dpContext;
+            typedef std::remove_reference<decltype(getDpScoreMatrix(dpContext))>::type TScoreHost;
+            typedef std::remove_reference<decltype(getDpTraceMatrix(dpContext))>::type TTraceHost;
+            typedef DPMatrix_<TCell, SparseDPMatrix, TScoreHost> TDPScoreMatrix;
+            typedef DPMatrix_<TTraceValue, FullDPMatrix, TTraceHost> TDPTraceMatrix;
+            typedef DPMatrixNavigator_<TDPScoreMatrix, DPScoreMatrix, NavigateColumnWise> TScoreNav;
+            typedef DPMatrixNavigator_<TDPTraceMatrix, DPTraceMatrix<TracebackOn<TracebackConfig_<SingleTrace, GapsLeft> > >, NavigateColumnWise> TTraceNav;
+            typedef DPScout_<TCell, Default> TDPScout;
+            DPBandConfig<BandOff> band;
+            TDPScoreMatrix dpScoreMatrix; TDPTraceMatrix dpTraceMatrix;
+            setLength(dpScoreMatrix, +DPMatrixDimension_::HORIZONTAL, length(seqH) + 1);
+            setLength(dpTraceMatrix, +DPMatrixDimension_::HORIZONTAL, length(seqH) + 1);
+            setLength(dpScoreMatrix, +DPMatrixDimension_::VERTICAL, length(seqV) + 1);
+            setLength(dpTraceMatrix, +DPMatrixDimension_::VERTICAL, length(seqV) + 1);
+            setHost(dpScoreMatrix, getDpScoreMatrix(dpContext));
+            setHost(dpTraceMatrix, getDpTraceMatrix(dpContext));
+            resize(dpScoreMatrix); resize(dpTraceMatrix);
+            TScoreNav scoreNav{dpScoreMatrix, band};
+            TTraceNav traceNav{dpTraceMatrix, band};
+            DPScoutState_<Default> scoutState;
+            TDPScout dpScout(scoutState);
+            _computeAlignmentImpl(dpScout, scoreNav, traceNav, seqH, seqV, sc, band, TDPProfile(), NavigateColumnWise{});
+            TTraceHost & th = getDpTraceMatrix(dpContext);
+            std::cout << "GFILL score=" << maxScore(dpScout) << " S=" << _scoreOfCell(dpScout._maxScore) << " H="
+                      << _horizontalScoreOfCell(dpScout._maxScore) << " V=" << _verticalScoreOfCell(dpScout._maxScore)
+                      << " pos=" << dpScout._maxHostPosition << " tracelen=" << length(th) << " hash="
+                      << fnv1a((unsigned char const *)&th[0], length(th) * sizeof(TTraceValue));
+            // and the fragments the library call returns
+            String<Fragment<> > matches;
+            StringSet<Dna5String, Dependent<> > pairSet; appendValue(pairSet, seqH); appendValue(pairSet, seqV);
+            int sc2 = globalAlignment(matches, pairSet, sc, AlignConfig<>(), Gotoh());
+            std::cout << " libscore=" << sc2 << " frags=";
+            for (unsigned i = 0; i < length(matches); ++i)
+                std::cout << (i ? "," : "") << matches[i].begin1 << ":" << matches[i].begin2 << ":" << matches[i].len;
             std::cout << "\n";
         }
         else if (cmd == "MERGE")

@@ -62,6 +62,15 @@ class BamRecord(C.Structure):
                 ("seq", C.c_char_p), ("seq_len", C.c_int32)]
 
 
+class MsaPair(C.Structure):
+    _fields_ = [("h", u8p), ("n", C.c_int32), ("v", u8p), ("m", C.c_int32)]
+
+
+class MsaFillResult(C.Structure):
+    _fields_ = [("score", C.c_int32), ("row", C.c_int32), ("col", C.c_int32), ("dir", C.c_int32), ("S", C.c_int32),
+                ("H", C.c_int32), ("V", C.c_int32)]
+
+
 class FinalIn(C.Structure):
     _fields_ = [("ref_part", u8p), ("ref_part_len", C.c_int32), ("seq", u8p), ("seq_len", C.c_int32)]
 
@@ -71,7 +80,7 @@ EXPORTS = ["svp_create", "svp_destroy", "svp_last_error", "svp_version", "svp_al
            "svp_debug_round", "svp_probe_dpx", "svp_stats", "svp_set_lanes", "svp_refine_variant", "svp_refine_info",
            "svp_format_quality", "svp_record_supports_variant", "svp_read_region_boundaries",
            "svp_alignment_length_in_ref", "svp_cut_down_high_coverage", "svp_merge_record_group", "svp_k1_cells",
-           "svp_flush", "svp_final_align_static", "svp_probe_fp64", "svp_engine_config", "svp_engine_stats", "svp_window_capacity"]
+           "svp_flush", "svp_msa_begin", "svp_msa_global_fill", "svp_msa_local_fill", "svp_final_align_static", "svp_probe_fp64", "svp_engine_config", "svp_engine_stats", "svp_window_capacity"]
 
 _lib = None
 
@@ -103,6 +112,10 @@ def lib():
         L.svp_submit_polish.argtypes = [C.c_void_p, C.c_uint64, C.POINTER(WindowIn), C.POINTER(Result)]
         L.svp_wait_any.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.POINTER(Result))]
         L.svp_flush.argtypes = [C.c_void_p]
+        L.svp_msa_begin.argtypes = [C.c_void_p, C.c_int32, C.POINTER(MsaPair), C.c_int32, C.c_int32, C.c_int32, C.c_int32]
+        L.svp_msa_global_fill.argtypes = [C.c_void_p, C.c_int32, i32p, C.POINTER(u8p), C.POINTER(MsaFillResult)]
+        L.svp_msa_local_fill.argtypes = [C.c_void_p, C.c_int32, i32p, C.POINTER(i32p), i32p, C.POINTER(u8p),
+                                         C.POINTER(MsaFillResult)]
         L.svp_final_align_static.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p,
                                              C.c_int32, C.c_void_p]
         L.svp_engine_config.argtypes = [C.c_void_p, C.c_int32, C.c_int32]
@@ -458,6 +471,41 @@ class Context:
         return dict(profile=prof[:n].copy(), cov=cov[:n].copy(), isgap=isgap[:n].copy(),
                     proper=proper[:len(v["reads1"])].copy(), out=seq[:olen.value].copy(), mappQ_mean=mq.value,
                     subst=int(cnt[0]), ins=int(cnt[1]), dele=int(cnt[2]), baseQ_mean=w.baseQ_mean)
+
+    # ---- pairwise fills of build_consensus (svp_msa_*) ---------------------------------------------
+    def msa_begin(self, pairs, scores=(5, -3, -1, -3)):
+        """pairs: [(h, v)] uint8 arrays (h = columns = str[0], v = rows = str[1])"""
+        self._msa_keep = [(np.ascontiguousarray(h, np.uint8), np.ascontiguousarray(v, np.uint8)) for h, v in pairs]
+        arr = (MsaPair * len(pairs))(*[MsaPair(_p(h), len(h), _p(v), len(v)) for h, v in self._msa_keep])
+        self._check(self.L.svp_msa_begin(self.h, len(pairs), arr, *scores), "svp_msa_begin")
+
+    def _msa_fill(self, local, idx, new_cells):
+        n = len(idx)
+        ia = np.ascontiguousarray(idx, np.int32)
+        sizes = []
+        for p in idx:
+            h, v = self._msa_keep[p]
+            sizes.append(len(h) * ((len(v) + 1) // 2) if local else (len(h) + 1) * (len(v) + 1))
+        bufs = [np.zeros(max(1, sz), np.uint8) for sz in sizes]
+        tp = (u8p * n)(*[_p(b) for b in bufs])
+        res = (MsaFillResult * n)()
+        if local:
+            cells = [np.ascontiguousarray(np.array(c, np.int32).reshape(-1), np.int32) if len(c) else np.zeros(2, np.int32)
+                     for c in (new_cells or [[]] * n)]
+            cp = (i32p * n)(*[_p(c, i32p) for c in cells])
+            nn = np.array([len(c) for c in (new_cells or [[]] * n)], np.int32)
+            rc = self.L.svp_msa_local_fill(self.h, n, _p(ia, i32p), cp, _p(nn, i32p), tp, res)
+        else:
+            rc = self.L.svp_msa_global_fill(self.h, n, _p(ia, i32p), tp, res)
+        self._check(rc, "svp_msa_local_fill" if local else "svp_msa_global_fill")
+        return [(b[:sz], dict(score=r.score, row=r.row, col=r.col, dir=r.dir, S=r.S, H=r.H, V=r.V)) for b, sz, r in zip(bufs, sizes, res)]
+
+    def msa_global_fill(self, idx):
+        return self._msa_fill(False, idx, None)
+
+    def msa_local_fill(self, idx, new_cells=None):
+        """new_cells: per listed pair, [(col, row), ...] to forbid before this round"""
+        return self._msa_fill(True, idx, new_cells)
 
     def probe_dpx(self):
         a, b, c = C.c_double(), C.c_double(), C.c_double()

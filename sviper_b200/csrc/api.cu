@@ -19,6 +19,7 @@ static svp_ctx *make_ctx(int cuda_device, void *cuda_stream, bool is_lane);
 #include "api_align.inc"
 #include "api_polish.inc"
 #include "api_final.inc"
+#include "api_msa.inc"
 #include "api_eval.inc"
 #include "api_prepare.inc"
 #include "api_merge.inc"
@@ -140,6 +141,7 @@ void svp_destroy(svp_ctx *ctx)
 {
     if (!ctx) return;
     engine_stop(ctx);
+    if (cudaSetDevice(ctx->device) != cudaErrorCudartUnloading) msa_release(ctx);
     if (cudaSetDevice(ctx->device) == cudaErrorCudartUnloading)
     {
         // process exit: the CUDA runtime is already gone (a context held by a static object); nothing left to free

@@ -9,6 +9,7 @@
 #include "k1_trace.cuh"
 #include "k3_pileup.cuh"
 #include "k5_final.cuh"
+#include "k6_msa.cuh"
 
 struct DevBuf
 {
@@ -94,6 +95,7 @@ struct DevSeqs
 struct PolishLayout;
 struct FinalSpec;
 struct svp_engine;
+struct MsaSession;
 
 constexpr int SVP_DEFAULT_LANES = 4, SVP_MAX_LANES = 16, SVP_MIN_PER_LANE = 4;
 
@@ -161,6 +163,8 @@ struct svp_ctx
     int64_t est_units = 0, est_words = 0;   // first-round estimate of the current batch (polish_upload / upload_tasks)
     // ---- asynchronous batch scheduler (api_final.inc): one worker thread per lane ----
     struct svp_engine *engine = nullptr;
+    // ---- pairwise fills of build_consensus (api_msa.inc) ----
+    struct MsaSession *msa = nullptr;
 };
 
 static int svp_fail(svp_ctx *ctx, cudaError_t e, const char *what, const char *file, int line)

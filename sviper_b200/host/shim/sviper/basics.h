@@ -10,6 +10,28 @@
 // ONE device job instead of two round trips.
 #pragma once
 
+// build_consensus (basics.h:484-520) stays the reference's code; the library call in it,
+// seqan::globalMsaAlignment(align, seqan::SimpleScore(5, -3, -1, -3)) (basics.h:494), resolves to the overload below
+// (declared before the reference's header is read, preferred over SeqAn's template by overload resolution): the same stages
+// with SeqAn's own functions, the pairwise DP fills on the GPU (sviper_b200_msa.hpp). SVIPER_B200_MSA=host keeps SeqAn's
+// own globalMsaAlignment (A/B measurements of the whole program; the polishing hot path is on the GPU either way).
+#include "../sviper_b200_msa.hpp"
+
+namespace seqan
+{
+inline void globalMsaAlignment(Align<Dna5String, ArrayGaps> & align, Score<int, Simple> const & scoreObject)
+{
+    static bool const on_host = [] { char const * e = std::getenv("SVIPER_B200_MSA"); return e && std::string(e) == "host"; }();
+    if (on_host)
+    {
+        globalMsaAlignment<Dna5String, ArrayGaps, Score<int, Simple> >(align, scoreObject);   // SeqAn's template, unchanged
+        return;
+    }
+    sviper_b200::shim::DeviceFills fills;
+    sviper_b200::shim::global_msa_alignment(fills, align, scoreObject);
+}
+}  // namespace seqan
+
 #define append_ref_flanks append_ref_flanks_reference
 #include_next <sviper/basics.h>
 #undef append_ref_flanks
