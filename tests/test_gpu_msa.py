@@ -86,9 +86,9 @@ def test_fills_match_the_oracle_on_random_and_edge_shapes(ctx):
                 add.append((c, r)); r -= 1; c -= 1
             cells[k] = cells[k] + add
             new.append(add)
-    # a subset of the pairs, in another order, after the bitmaps have been used
+    # a subset of the pairs, in another order, after the bitmaps have been used (with the cells of the last round still to send)
     sub = [5, 2, len(pairs) - 1]
-    for g, k in zip(ctx.msa_local_fill(sub, [[] for _ in sub]), sub):
+    for g, k in zip(ctx.msa_local_fill(sub, [new[k] for k in sub]), sub):
         check_local(g, pairs[k][0], pairs[k][1], cells[k])
 
 
