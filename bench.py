@@ -228,7 +228,7 @@ def run_gpu(args):
     cores_per_rank = max(1, host_cores() // max(1, env_world))
     t0 = time.perf_counter()
     n_c3 = 0 if args.quick else args.c3_variants
-    c3_shard = bc.generate(bc.c3_variant, range(env_rank, n_c3, env_world), min(8, cores_per_rank)) if n_c3 else []
+    c3_shard = bc.generate(bc.c3_variant, bc.shard_records(n_c3, env_world)[env_rank], min(8, cores_per_rank)) if n_c3 else []
     c3_gen = time.perf_counter() - t0
     t0 = time.perf_counter()
     c4_list = bc.generate(bc.c4_variant, range(args.c4_variants), min(8, cores_per_rank)) if (single_extras and args.c4_variants) else []

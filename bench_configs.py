@@ -22,20 +22,23 @@ def host_cores():
         return os.cpu_count() or 1
 
 
+def c3_record(i):
+    """what the candidate VCF says about record i of configs[2]: (type, SVLEN)"""
+    rng = np.random.default_rng(3 * 1000003 + i)
+    return ("DEL" if i % 2 == 0 else "INS"), int(round(math.exp(rng.uniform(math.log(50), math.log(1000)))))
+
+
 def c3_variant(i):
     """configs[2]: 5,000 mixed DEL / INS of 50..1000 bp (log-uniform), -k 400; record i of the candidate list"""
     from sviper_b200 import synth
-    rng = np.random.default_rng(3 * 1000003 + i)
-    svlen = int(round(math.exp(rng.uniform(math.log(50), math.log(1000)))))
-    return synth.make_variant(3 * 100003 + i, "DEL" if i % 2 == 0 else "INS", svlen=svlen, k=K_FLANK, cov=COV, cons_err=0.05)
+    kind, svlen = c3_record(i)
+    return synth.make_variant(3 * 100003 + i, kind, svlen=svlen, k=K_FLANK, cov=COV, cons_err=0.05)
 
 
-def c4_variant(i):
-    """configs[3]: insertions of 1..10 kb (log-uniform), -k 1000: windows of 4..13 kb"""
-    from sviper_b200 import synth
-    rng = np.random.default_rng(4 * 1000003 + i)
-    svlen = int(round(math.exp(rng.uniform(math.log(1000), math.log(10000)))))
-    return synth.make_variant(4 * 100003 + i, "INS", svlen=svlen, k=1000, cov=COV, cons_err=0.05)
+def shard_records(n_total, world):
+    """which records of configs[2] each rank polishes: sviper_b200.shard.deal on the work the candidate VCF lets one estimate"""
+    from sviper_b200 import shard
+    return shard.deal([shard.window_work(*c3_record(i), flanking_region=K_FLANK) for i in range(n_total)], world)
 
 
 def generate(fn, indices, procs):
@@ -130,14 +133,16 @@ def pack_results(res):
 
 
 def run_sharded_c3(ctx, rank, world, flush, gloo, n_total, shard, t_gen, barrier, max_over_ranks, sum_over_ranks):
-    """BASELINE.json configs[2] as north_star states it: ONE candidate list of n_total mixed DEL / INS records, record i
-    polished by rank i mod N (block-cyclic, so DEL and INS windows spread evenly), no data-path collective; rank 0 gathers
+    """BASELINE.json configs[2] as north_star states it: ONE candidate list of n_total mixed DEL / INS records, dealt to the
+    ranks by shard_records() (balanced by the work the VCF lets one estimate), no data-path collective; rank 0 gathers
     every rank's results on the HOST and puts them into input order (the reference writes its VCF in input order from one
     vector, io.h:89-90). Strong scaling: total work is fixed. Timed end to end -- host buffers in, results gathered on
     rank 0 -- and, separately, HBM-resident (device events, max over ranks)."""
     import pickle
     import torch
     import torch.distributed as dist
+    owners = shard_records(n_total, world)
+    assert len(owners[rank]) == len(shard)
     ctx.set_lanes(4)
     pb = ctx.prepare(shard, with_final=True)
     ctx.run_prepared(pb)                                   # warm-up: sizes every arena for this shard
@@ -151,15 +156,22 @@ def run_sharded_c3(ctx, rank, world, flush, gloo, n_total, shard, t_gen, barrier
         t_dev = time.perf_counter() - t0
         blob = pack_results(ctx.collect(pb))
         if world > 1:
-            parts = [None] * world if rank == 0 else None
-            dist.gather_object(blob, parts, dst=0, group=gloo)
+            # host gather to rank 0 (gloo): sizes first, then the byte blobs as padded uint8 tensors
+            mine = torch.frombuffer(bytearray(blob), dtype=torch.uint8)
+            sizes = [torch.zeros(1, dtype=torch.int64) for _ in range(world)]
+            dist.all_gather(sizes, torch.tensor([mine.numel()], dtype=torch.int64), group=gloo)
+            cap = int(max(int(x) for x in sizes))
+            padded = torch.zeros(cap, dtype=torch.uint8); padded[:mine.numel()] = mine
+            bufs = [torch.zeros(cap, dtype=torch.uint8) for _ in range(world)] if rank == 0 else None
+            dist.gather(padded, bufs, dst=0, group=gloo)
+            parts = [bytes(b[:int(n)].numpy()) for b, n in zip(bufs, sizes)] if rank == 0 else None
         else:
             parts = [blob]
         if rank == 0:
             out = [None] * n_total
             for r, part in enumerate(parts):
-                for j, item in enumerate(pickle.loads(part)):
-                    out[r + j * world] = item          # input order
+                for j, item in zip(owners[r], pickle.loads(part)):
+                    out[j] = item                      # input order
             assert all(x is not None for x in out)
             gathered = out
         times.append((time.perf_counter() - t0, t_dev))
@@ -177,7 +189,8 @@ def run_sharded_c3(ctx, rank, world, flush, gloo, n_total, shard, t_gen, barrier
     if rank != 0:
         return None
     return {"workload": "BASELINE.json configs[2]: one candidate list of %d mixed DEL/INS (50-1000 bp, 30x 2x150 bp, -k 400), "
-                        "record i on rank i mod N, results gathered on the host of rank 0 into input order" % n_total,
+                        "dealt to the ranks in order of decreasing estimated work (snake), results gathered on the host of rank 0 into "
+                        "input order" % n_total,
             "scaling": "strong", "variants": n_total, "n_gpus": world,
             "e2e_variants_per_s": n_total / e2e_s, "e2e_seconds": e2e_s,
             "e2e_includes": "staging + H2D + all kernels + D2H per rank, pickling, gloo gather to rank 0, reordering",
