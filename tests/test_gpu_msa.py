@@ -99,8 +99,9 @@ def test_fill_arguments_are_checked(ctx):
     bad = (api.MsaPair * 1)(api.MsaPair(api._p(a), 3, api._p(a), 0))
     assert ctx.L.svp_msa_begin(ctx.h, 1, bad, 5, -3, -1, -3) == -2
     ctx.msa_begin([(a, a)])
-    with pytest.raises(RuntimeError):
-        ctx.msa_local_fill([3])
+    tp = (api.u8p * 1)(api._p(np.zeros(16, np.uint8)))
+    res = (api.MsaFillResult * 1)()
+    assert ctx.L.svp_msa_local_fill(ctx.h, 1, api._p(np.array([3], np.int32), api.i32p), None, None, tp, res) == -2   # no such pair
     with pytest.raises(RuntimeError):
         ctx.msa_local_fill([0], [[(9, 1)]])
     trace, res = ctx.msa_local_fill([0])[0]
