@@ -335,7 +335,7 @@ def run_gpu(args):
     for _ in range(2):
         ctx.polish_rerun()
     ctx.stats(reset=1); ctx.stats(reset=2)
-    ctx.k1_cells(reset=1)
+    ctx.k1_cells(reset=1); ctx.k1_failed_certificates(reset=1)
     single_ms = []
     for _ in range(args.steps):
         flush.zero_()
@@ -347,6 +347,7 @@ def run_gpu(args):
     _, kms = ctx.stats(reset=1)
     k1_reg_cells, k1_mix_cells = ctx.k1_cells(reset=1, split=True)   # cells the score kernel computed in the per-kernel pass
     k1_computed = k1_reg_cells + k1_mix_cells
+    k1_failed = ctx.k1_failed_certificates(reset=1)
     ctx.stats(reset=3)
     sampler.stop_flag = True; sampler.join(timeout=3)
     clocks = sampler.summary()
@@ -431,7 +432,8 @@ def run_gpu(args):
                                                   "(k1_score_kernel<.,.,mixed>) + the remaining regular tasks",
                                           "ms_per_step": kms["k1_score_mixed"] / args.steps,
                                           "cells_computed_per_step": k1_mix_cells / args.steps,
-                                          "gcups": (k1_mix_cells / (kms["k1_score_mixed"] * 1e-3) / 1e9) if kms["k1_score_mixed"] else None},
+                                          "gcups": (k1_mix_cells / (kms["k1_score_mixed"] * 1e-3) / 1e9) if kms["k1_score_mixed"] else None,
+                                          "certificates_failed_inside_a_mixed_launch_per_step": k1_failed / args.steps},
                          "score_pass_cells_computed_over_algorithmic": k1_computed / float(cells * args.steps) if cells else None,
                          "timed": "single-part pass of the same steps (svp_set_lanes(1)): %.3f ms per step" %
                                   (sum(single_ms) / args.steps),

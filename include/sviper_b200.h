@@ -347,6 +347,10 @@ int svp_debug_round(svp_ctx *ctx, const svp_window_in *w, int fix_indels, double
  * cells[1] in mixed rounds (a pair's two known strands as one task: half of that). Synchronises the context's streams. */
 int svp_k1_cells(svp_ctx *ctx, double *cells /* 2 entries */, int reset);
 
+/* Reads whose strand certificate failed INSIDE a mixed launch since the last reset (they are re-aligned on both strands by a
+ * further launch behind it; reads expected to fail are sent to the regular list up front and are not counted). */
+int svp_k1_failed_certificates(svp_ctx *ctx, double *reads, int reset);
+
 /* Measures the sustained rate of the DPX-class packed 16x2 instructions the score kernel is made of
  * (VIADDMNMX / VIMNMX3 / IADD), in lane-operations per second over the whole chip. */
 int svp_probe_dpx(svp_ctx *ctx, double *viaddmax_lane_ops, double *vimax3_lane_ops, double *mix_lane_ops);

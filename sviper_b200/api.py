@@ -80,7 +80,7 @@ EXPORTS = ["svp_create", "svp_destroy", "svp_last_error", "svp_version", "svp_al
            "svp_debug_round", "svp_probe_dpx", "svp_stats", "svp_set_lanes", "svp_refine_variant", "svp_refine_info",
            "svp_format_quality", "svp_record_supports_variant", "svp_read_region_boundaries",
            "svp_alignment_length_in_ref", "svp_cut_down_high_coverage", "svp_merge_record_group", "svp_k1_cells",
-           "svp_flush", "svp_msa_begin", "svp_msa_global_fill", "svp_msa_local_fill", "svp_final_align_static", "svp_probe_fp64", "svp_engine_config", "svp_engine_stats", "svp_window_capacity"]
+           "svp_flush", "svp_k1_failed_certificates", "svp_msa_begin", "svp_msa_global_fill", "svp_msa_local_fill", "svp_final_align_static", "svp_probe_fp64", "svp_engine_config", "svp_engine_stats", "svp_window_capacity"]
 
 _lib = None
 
@@ -136,6 +136,7 @@ def lib():
         L.svp_alignment_length_in_ref.argtypes = [C.c_char_p, u32p, C.c_int32]
         L.svp_cut_down_high_coverage.argtypes = [C.c_int32, i32p, u8p, i32p, C.c_int32, i32p]
         L.svp_k1_cells.argtypes = [C.c_void_p, f64p, C.c_int]
+        L.svp_k1_failed_certificates.argtypes = [C.c_void_p, f64p, C.c_int]
         L.svp_merge_record_group.argtypes = [C.c_int32, C.POINTER(BamRecord), i32p, i32p, C.c_char_p, u32p, C.c_int32, i32p,
                                              C.c_char_p, C.c_int32, i32p]
         _lib = L
@@ -522,6 +523,11 @@ class Context:
         v = (C.c_double * 2)()
         self._check(self.L.svp_k1_cells(self.h, v, reset), "svp_k1_cells")
         return v[0] + v[1] if not split else (v[0], v[1])
+
+    def k1_failed_certificates(self, reset=0):
+        v = C.c_double()
+        self._check(self.L.svp_k1_failed_certificates(self.h, C.byref(v), reset), "svp_k1_failed_certificates")
+        return v.value
 
     def set_lanes(self, n):
         """number of concurrent parts a polish batch is split into on this GPU (svp_set_lanes)"""

@@ -360,6 +360,24 @@ int svp_k1_cells(svp_ctx *ctx, double *cells, int reset)
     return SVP_OK;
 }
 
+int svp_k1_failed_certificates(svp_ctx *ctx, double *reads, int reset)
+{
+    if (!ctx || !reads) return SVP_ERR_ARG;
+    std::vector<svp_ctx *> all(1, ctx);
+    all.insert(all.end(), ctx->lanes.begin(), ctx->lanes.end());
+    *reads = 0;
+    for (svp_ctx *c : all)
+    {
+        if (!c->mixcnt.p || !c->mixcnt_zeroed) continue;
+        unsigned long long v = 0;
+        CK(cudaStreamSynchronize(c->stream));
+        CK(cudaMemcpy(&v, c->mixcnt.as<char>() + 56, 8, cudaMemcpyDeviceToHost));
+        *reads += (double)v;
+        if (reset) CK(cudaMemset(c->mixcnt.as<char>() + 56, 0, 8));
+    }
+    return SVP_OK;
+}
+
 double svp_assign_quality(int32_t n_cigar, int32_t flanking_region)
 {
     double error_rate = ((double)n_cigar - 1.0) / (flanking_region * 2.0);

@@ -69,7 +69,8 @@ struct K1Mix
 {
     const int32_t *n_dev;      // number of tasks (pairs if MIXED) of this launch, on the device; null: `ntasks`
     int32_t *sstate;           // per task: bit 0 strand known, bit 1 is_rc, bit 2 weak (winner scored < K1_WEAK: its certificate
-                               // would probably fail again), bits 16..31 bound on the other strand's score
+                               // would probably fail again), bits 3..12 the winner's last score (clamped to 0..1023; only used
+                               // to PREDICT the certificate, never to decide it), bits 16..31 bound on the other strand's score
     const int32_t *emax;       // per window: edit cost E for W = 320, W = 512
     int32_t *fb19, *fb32;      // lists the failed certificates are appended to (both strands again, same round)
     int32_t *fb_cnt;           // their counters [2]
@@ -281,7 +282,8 @@ __global__ void __launch_bounds__(THREADS, 512 / THREADS) k1_score_kernel(const 
                 int lose = rc ? s_lo : s_hi;
                 lose = max(-32768, min(32767, lose));
                 const int win = rc ? s_hi : s_lo;
-                mix.sstate[task] = (int32_t)(((uint32_t)lose << 16) | (uint32_t)(rc << 1) | 1u | (win < K1_WEAK ? 4u : 0u));
+                mix.sstate[task] = (int32_t)(((uint32_t)lose << 16) | (uint32_t)(rc << 1) | 1u | (win < K1_WEAK ? 4u : 0u) |
+                                             ((uint32_t)max(0, min(1023, win)) << 3));
             }
             if (mix.cells) atomicAdd(mix.cells, 2ull * (unsigned long long)R * (unsigned long long)L);
         }
@@ -300,17 +302,19 @@ __global__ void __launch_bounds__(THREADS, 512 / THREADS) k1_score_kernel(const 
                     o.score_f = rc ? nb : sc; o.score_r = rc ? sc : nb;   // the loser's entry is only ever compared
                     o.col_f = rc ? 0 : col; o.col_r = rc ? col : 0;
                     out[t] = o;
-                    mix.sstate[t] = (int32_t)(((uint32_t)nb << 16) | (uint32_t)(rc << 1) | 1u | (sc < K1_WEAK ? 4u : 0u));
+                    mix.sstate[t] = (int32_t)(((uint32_t)nb << 16) | (uint32_t)(rc << 1) | 1u | (sc < K1_WEAK ? 4u : 0u) |
+                                              ((uint32_t)max(0, min(1023, sc)) << 3));
                 }
                 else
                 {
                     mix.sstate[t] = 0;
+                    if (mix.cells) atomicAdd(mix.cells + 2, 1ull);                   // statistics: certificates that failed in a mixed launch
                     const int cls = Rt > 152;
                     const int at = atomicAdd(mix.fb_cnt + cls, 1);
                     (cls ? mix.fb32 : mix.fb19)[at] = t;
                 }
             }
-            if (mix.cells) atomicAdd(mix.cells, (unsigned long long)(R + R2) * (unsigned long long)L);
+            if (mix.cells) atomicAdd(mix.cells, (unsigned long long)(R + R2) * (unsigned long long)L);   // (mix.cells points at the mixed-round counter)
         }
     }
 }
@@ -320,6 +324,7 @@ __global__ void __launch_bounds__(THREADS, 512 / THREADS) k1_score_kernel(const 
 __global__ void mix_plan_kernel(const int32_t *__restrict__ pair_task, int64_t npairs, const int32_t *__restrict__ task_read,
                                 const int32_t *__restrict__ task_win, const int32_t *__restrict__ read_len,
                                 const uint8_t *__restrict__ win_done, const int32_t *__restrict__ sstate,
+                                const int32_t *__restrict__ emax,
                                 int32_t *__restrict__ reg19, int32_t *__restrict__ reg32, int32_t *__restrict__ mix19,
                                 int32_t *__restrict__ mix32, int32_t *__restrict__ cnt)
 {
@@ -330,7 +335,18 @@ __global__ void mix_plan_kernel(const int32_t *__restrict__ pair_task, int64_t n
     if (win_done[task_win[t1]]) return;
     const int R1 = read_len[task_read[t1]], R2 = t2 >= 0 ? read_len[task_read[t2]] : 0;
     const int s1 = sstate[t1], s2 = t2 >= 0 ? sstate[t2] : 0;
-    if (t2 >= 0 && (s1 & 1) && (s2 & 1) && !((s1 | s2) & 4))
+    // Will the certificate hold? The mixed launch accepts a read iff its new score S satisfies S >= 0 and S > max(bound + E, -6)
+    // (E = emax of its window). S is not known yet, but polishing rarely lowers a read's score, so a read whose LAST score (less
+    // a small margin) does not clear bound + E is expected to fail and goes to the regular list right away -- that list runs
+    // BESIDE the mixed launch, whereas a failure inside it costs another launch behind it. Only a prediction: a wrong guess
+    // either way changes where the read is aligned, never the result. (Predicting with last - E, the worst case, sent most
+    // reads of round 2 to the regular list: 2.29 vs 1.89 ms per step.)
+    auto shaky = [&](int st, int R) {
+        const int e = emax[2 * task_win[t1] + (R > 152)];
+        const int last = (st >> 3) & 1023, bound = st >> 16;
+        return (st & 4) || (last - 8) <= max(bound + e, -6);
+    };
+    if (t2 >= 0 && (s1 & 1) && (s2 & 1) && !shaky(s1, R1) && !shaky(s2, R2))
     {
         const int cls = (R1 > 152 || R2 > 152);
         const int at = atomicAdd(cnt + 2 + cls, 1);

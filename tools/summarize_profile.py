@@ -18,7 +18,9 @@ BENCH_KEY = {"k1_score_kernel": "k1_score", "k1_band_kernel": "k1_trace", "k1_tr
              "k2_traceback_kernel": "k2_traceback", "k3_pileup_vote_kernel": "k3_pileup_vote",
              "k5_final_kernel": "k5_final", "k5_traceback_kernel": "k5_traceback", "pack_kernel": "pack",
              "window_refresh_kernel": "pack", "k1_score_kernel (mixed rounds)": "k1_score_mixed",
-             "mix_plan_kernel": "k1_score_mixed"}
+             "mix_plan_kernel": "k1_score_mixed", "plan_kernel": "other", "scan2_fit_kernel": "other", "fit_kernel": "other",
+             "DeviceScanKernel": "other", "DeviceScanInitKernel": "other", "count_active_kernel": "k3_pileup_vote",
+             "gather_kernel": "other"}
 RAW_KEEP = ["gpu__time_duration.sum", "launch__grid_size", "launch__block_size", "launch__registers_per_thread",
             "launch__occupancy_limit_shared_mem", "launch__occupancy_limit_registers",
             "sm__warps_active.avg.per_cycle_active", "smsp__issue_active.avg.per_cycle_active",
@@ -58,11 +60,11 @@ def read_launches(path):
 
 
 def last_step(seq):
-    """the launches of the last HBM-resident step: between the two last k5_traceback_kernel launches"""
+    """the launches of the last HBM-resident step: between the two last k5_traceback_kernel launches (a rerun has no gather)"""
     idx = [i for i, (k, _, _) in enumerate(seq) if "k5_traceback_kernel" in k]
     if len(idx) < 2:
         return seq
-    return seq[idx[-2] + 1: idx[-1] + 1]
+    return [x for x in seq[idx[-2] + 1: idx[-1] + 1] if "gather_kernel" not in x[0]]
 
 
 def raw_page(rep):
