@@ -41,6 +41,14 @@ def shard_records(n_total, world):
     return shard.deal([shard.window_work(*c3_record(i), flanking_region=K_FLANK) for i in range(n_total)], world)
 
 
+def c4_variant(i):
+    """configs[3]: insertions of 1..10 kb (log-uniform), -k 1000: windows of 4..13 kb"""
+    from sviper_b200 import synth
+    rng = np.random.default_rng(4 * 1000003 + i)
+    svlen = int(round(math.exp(rng.uniform(math.log(1000), math.log(10000)))))
+    return synth.make_variant(4 * 100003 + i, "INS", svlen=svlen, k=1000, cov=COV, cons_err=0.05)
+
+
 def generate(fn, indices, procs):
     """synthetic variants from forked worker processes (call this BEFORE the process touches CUDA / NCCL)"""
     indices = list(indices)
@@ -125,11 +133,38 @@ class GpuBusySampler(threading.Thread):
         return float(np.max(self.vals)) if self.vals else None
 
 
-def pack_results(res):
-    """what a rank hands to the gather: polished sequences, CIGARs and counters of its shard, as one byte string"""
-    import pickle
-    return pickle.dumps([(r["polished"].tobytes(), r.get("cigar", []), r["rounds"], r["subst"], r["ins"], r["dele"]) for r in res],
-                        protocol=pickle.HIGHEST_PROTOCOL)
+def pack_shard(pb):
+    """What a rank hands to the gather, straight from the caller-side result buffers of a prepared batch (no per-variant
+    Python objects): one uint8 array = header | polished lengths | CIGAR lengths | counters | polished bases | CIGAR ops |
+    CIGAR counts."""
+    n = pb["n"]
+    res = pb["res"]
+    plen = np.fromiter((res[i].polished_len for i in range(n)), np.int32, n)
+    ncig = np.fromiter((res[i].n_cigar for i in range(n)), np.int32, n)
+    cnt4 = np.fromiter((x for i in range(n) for x in (res[i].rounds, res[i].substituted_bases, res[i].inserted_bases,
+                                                      res[i].deleted_bases)), np.int32, 4 * n)
+    if any(res[i].status != 0 for i in range(n)):
+        raise RuntimeError("a variant of the shard failed")
+    pol = np.concatenate([pb["parts"][i][1][:plen[i]] for i in range(n)]) if n else np.zeros(0, np.uint8)
+    ops = np.concatenate([np.frombuffer(pb["parts"][i][3], np.uint8, int(ncig[i])) for i in range(n)]) if n else np.zeros(0, np.uint8)
+    cnts = np.concatenate([pb["parts"][i][4][:ncig[i]] for i in range(n)]) if n else np.zeros(0, np.uint32)
+    head = np.array([n, len(pol), len(ops)], np.int64)
+    return np.concatenate([head.view(np.uint8), plen.view(np.uint8), ncig.view(np.uint8), cnt4.view(np.uint8), pol, ops,
+                           cnts.astype(np.uint32).view(np.uint8)])
+
+
+def unpack_shard(buf):
+    """-> list of (polished bases, CIGAR ops, CIGAR counts, (rounds, subst, ins, del)) views, in shard order"""
+    n, npol, nops = (int(x) for x in buf[:24].view(np.int64))
+    o = 24
+    plen = buf[o:o + 4 * n].view(np.int32); o += 4 * n
+    ncig = buf[o:o + 4 * n].view(np.int32); o += 4 * n
+    cnt4 = buf[o:o + 16 * n].view(np.int32).reshape(n, 4); o += 16 * n
+    pol = buf[o:o + npol]; o += npol
+    ops = buf[o:o + nops]; o += nops
+    cnts = buf[o:o + 4 * nops].view(np.uint32)
+    pe, ce = np.cumsum(plen), np.cumsum(ncig)
+    return [(pol[pe[i] - plen[i]:pe[i]], ops[ce[i] - ncig[i]:ce[i]], cnts[ce[i] - ncig[i]:ce[i]], cnt4[i]) for i in range(n)]
 
 
 def run_sharded_c3(ctx, rank, world, flush, gloo, n_total, shard, t_gen, barrier, max_over_ranks, sum_over_ranks):
@@ -138,7 +173,6 @@ def run_sharded_c3(ctx, rank, world, flush, gloo, n_total, shard, t_gen, barrier
     every rank's results on the HOST and puts them into input order (the reference writes its VCF in input order from one
     vector, io.h:89-90). Strong scaling: total work is fixed. Timed end to end -- host buffers in, results gathered on
     rank 0 -- and, separately, HBM-resident (device events, max over ranks)."""
-    import pickle
     import torch
     import torch.distributed as dist
     owners = shard_records(n_total, world)
@@ -154,23 +188,22 @@ def run_sharded_c3(ctx, rank, world, flush, gloo, n_total, shard, t_gen, barrier
         t0 = time.perf_counter()
         ctx.run_prepared(pb)                               # host buffers -> device -> host buffers, 4 lanes
         t_dev = time.perf_counter() - t0
-        blob = pack_results(ctx.collect(pb))
+        mine = torch.from_numpy(pack_shard(pb))
         if world > 1:
-            # host gather to rank 0 (gloo): sizes first, then the byte blobs as padded uint8 tensors
-            mine = torch.frombuffer(bytearray(blob), dtype=torch.uint8)
+            # host gather to rank 0 (gloo): sizes first, then the byte arrays as padded uint8 tensors
             sizes = [torch.zeros(1, dtype=torch.int64) for _ in range(world)]
             dist.all_gather(sizes, torch.tensor([mine.numel()], dtype=torch.int64), group=gloo)
             cap = int(max(int(x) for x in sizes))
             padded = torch.zeros(cap, dtype=torch.uint8); padded[:mine.numel()] = mine
             bufs = [torch.zeros(cap, dtype=torch.uint8) for _ in range(world)] if rank == 0 else None
             dist.gather(padded, bufs, dst=0, group=gloo)
-            parts = [bytes(b[:int(n)].numpy()) for b, n in zip(bufs, sizes)] if rank == 0 else None
+            parts = [b[:int(n)].numpy() for b, n in zip(bufs, sizes)] if rank == 0 else None
         else:
-            parts = [blob]
+            parts = [mine.numpy()]
         if rank == 0:
             out = [None] * n_total
             for r, part in enumerate(parts):
-                for j, item in zip(owners[r], pickle.loads(part)):
+                for j, item in zip(owners[r], unpack_shard(part)):
                     out[j] = item                      # input order
             assert all(x is not None for x in out)
             gathered = out
@@ -193,7 +226,8 @@ def run_sharded_c3(ctx, rank, world, flush, gloo, n_total, shard, t_gen, barrier
                         "input order" % n_total,
             "scaling": "strong", "variants": n_total, "n_gpus": world,
             "e2e_variants_per_s": n_total / e2e_s, "e2e_seconds": e2e_s,
-            "e2e_includes": "staging + H2D + all kernels + D2H per rank, pickling, gloo gather to rank 0, reordering",
+            "e2e_includes": "staging + H2D + all kernels + D2H per rank, packing the shard's results into one byte array, gloo "
+                            "gather to rank 0, reordering into input order",
             "gather_seconds_rank0": times[-1][0] - times[-1][1],
             "resident_variants_per_s": n_total / (max(all_ms) * 1e-3), "resident_ms_per_rank": all_ms,
             "rank_imbalance_max_over_mean": max(all_ms) / (sum(all_ms) / len(all_ms)),
