@@ -11,6 +11,7 @@
 #include <deque>
 #include <cub/device/device_scan.cuh>
 #include <nvtx3/nvToolsExt.h>
+#include <sched.h>
 #include "ctx.cuh"
 #include "k1_score.cuh"
 
@@ -110,9 +111,20 @@ static svp_ctx *make_ctx(int cuda_device, void *cuda_stream, bool is_lane)
     }
     if (cudaHostAlloc((void **)&ctx->h_ctl, 2 * sizeof(svp::RoundCtl), cudaHostAllocDefault) != cudaSuccess) { delete ctx; return nullptr; }
     memset(ctx->h_ctl, 0, 2 * sizeof(svp::RoundCtl));
-    for (int i = 0; i < 2; ++i) cudaEventCreateWithFlags(&ctx->ev_ctl[i], cudaEventDisableTiming);
+    {
+        // blocking waits when this process has few cores for its lane threads (see svp_sync)
+        cpu_set_t set;
+        int cores = 64;
+        if (sched_getaffinity(0, sizeof set, &set) == 0) cores = CPU_COUNT(&set);
+        ctx->blocking_sync = cores < 3 * SVP_DEFAULT_LANES;
+        if (const char *bs = getenv("SVP_BLOCKING_SYNC")) ctx->blocking_sync = atoi(bs) == 1;
+    }
+    const unsigned evf = cudaEventDisableTiming | (ctx->blocking_sync ? cudaEventBlockingSync : 0);
+    cudaEventCreateWithFlags(&ctx->ev_sync, evf);
+    for (int i = 0; i < 2; ++i) cudaEventCreateWithFlags(&ctx->ev_ctl[i], evf);
     if (const char *sr = getenv("SVP_SPECULATIVE_ROUNDS")) ctx->sync_rounds = atoi(sr) != 1;
     if (const char *kt = getenv("SVP_K1_THREADS")) ctx->k1_threads = atoi(kt);
+    if (const char *mr = getenv("SVP_MIX_REGULAR")) ctx->mix_reg_wide = std::string(mr) == "wide";
     if (const char *kg = getenv("SVP_K5_GLOBAL_TABLE")) ctx->k5_global_table = atoi(kg) == 1;
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) ctx->arena_budget = (size_t)(free_b * 0.6);
@@ -169,6 +181,7 @@ void svp_destroy(svp_ctx *ctx)
     ctx->fail19.release(); ctx->fail32.release(); ctx->sstate.release(); ctx->reg19.release(); ctx->reg32.release();
     ctx->mix19.release(); ctx->mix32.release(); ctx->mixcnt.release(); ctx->edit.release(); ctx->emax.release();
     for (int i = 0; i < 2; ++i) if (ctx->ev_ctl[i]) cudaEventDestroy(ctx->ev_ctl[i]);
+    if (ctx->ev_sync) cudaEventDestroy(ctx->ev_sync);
     ctx->stage.release();
     if (ctx->h_ctl) cudaFreeHost(ctx->h_ctl);
     delete ctx->resident;

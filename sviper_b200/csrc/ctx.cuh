@@ -140,6 +140,7 @@ struct svp_ctx
     DevBuf descs, states, states_init, pair_task, cons0, cons1, inslen, voff, profile, cov, isgap, decision, proper, cons_init;
     // strand certificates (k1_score.cuh, K1Mix): per-task strand state, per-round task lists, per-window edit density
     DevBuf sstate, reg19, reg32, mix19, mix32, fail19, fail32, mixcnt, edit, emax;
+    bool mix_reg_wide = false;              // SVP_MIX_REGULAR=wide: regular tasks of a mixed round in the wide shape (A/B switch)
     int k1_threads = 0;                     // 0: choose per launch; 64 / 128: force the block size of the throughput shape (SVP_K1_THREADS)
     bool mixcnt_zeroed = false;             // mixcnt: 4 list counters (reset every round) + the DP cell counter at byte 32
     int64_t pairs_total = 0, n_mateless = 0;   // pairs of the batch; pairs with a dummy mate
@@ -158,6 +159,8 @@ struct svp_ctx
     svp::RoundCtl *h_ctl = nullptr;          // pinned, 2 slots
     cudaEvent_t ev_ctl[2] = {nullptr, nullptr};
     int64_t cap_units = 0, cap_words = 0;   // what the per-round arenas (records, paths, trace) currently hold
+    bool blocking_sync = false;             // svp_sync: sleep instead of spin (SVP_BLOCKING_SYNC=0|1; default by core count)
+    cudaEvent_t ev_sync = nullptr;
     int n_regrow = 0;                       // rounds repeated because an arena had to grow
     bool sync_rounds = true;                // wait for the outcome of a round before queueing the next (SVP_SPECULATIVE_ROUNDS=1: one round ahead)
     int64_t est_units = 0, est_words = 0;   // first-round estimate of the current batch (polish_upload / upload_tasks)
@@ -166,6 +169,18 @@ struct svp_ctx
     // ---- pairwise fills of build_consensus (api_msa.inc) ----
     struct MsaSession *msa = nullptr;
 };
+
+// Waits for everything queued on the context's stream. On a host with few cores per GPU (8 ranks x 4 lane threads on 32
+// cores) the default spinning wait of the CUDA runtime lets the lane threads starve each other and the submitting thread;
+// there the wait goes through an event created with cudaEventBlockingSync (the thread sleeps). With cores to spare the
+// spinning wait is kept: it returns ~20 us sooner, several times per round.
+static inline cudaError_t svp_sync(svp_ctx *ctx)
+{
+    if (!ctx->blocking_sync) return cudaStreamSynchronize(ctx->stream);
+    cudaError_t e = cudaEventRecord(ctx->ev_sync, ctx->stream);
+    if (e != cudaSuccess) return e;
+    return cudaEventSynchronize(ctx->ev_sync);
+}
 
 static int svp_fail(svp_ctx *ctx, cudaError_t e, const char *what, const char *file, int line)
 {

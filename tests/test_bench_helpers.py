@@ -1,0 +1,49 @@
+"""CPU checks of the benchmark's host logic (bench.py / bench_configs.py): everything bench.py uses exists, the candidate list
+of configs[2] is dealt evenly, the shard packing for the host gather round-trips, the workload generators produce the shapes
+BASELINE.json names. (The timed paths need a GPU.)"""
+import ctypes as C
+import re
+
+import numpy as np
+
+
+def test_bench_uses_only_helpers_that_exist():
+    import bench
+    import bench_configs as bc
+    names = set(re.findall(r"\bbc\.([a-zA-Z_0-9]+)", open(bench.__file__).read()))
+    assert names and all(hasattr(bc, n) for n in names), sorted(n for n in names if not hasattr(bc, n))
+
+
+def test_workload_shapes():
+    import bench
+    import bench_configs as bc
+    v = bench.make_batch(2, seed=1000)[0]
+    assert v["kind"] == "DEL" and 50 <= v["svlen"] <= 1000 and 1700 <= len(v["consensus"]) <= 1900 and all(len(r) == 150 for r in v["reads1"])
+    kinds = [bc.c3_record(i)[0] for i in range(10)]
+    assert kinds.count("DEL") == 5 and kinds.count("INS") == 5
+    v3 = bc.c3_variant(1)
+    assert v3["kind"] == "INS" and v3["svlen"] == bc.c3_record(1)[1]
+    v4 = bc.c4_variant(0)
+    assert v4["kind"] == "INS" and 1000 <= v4["svlen"] <= 10000 and v4["k"] == 1000 and len(v4["consensus"]) >= 3900
+    shards = bc.shard_records(5000, 8)
+    assert sorted(i for s in shards for i in s) == list(range(5000)) and {len(s) for s in shards} == {625}
+
+
+def test_shard_packing_round_trip():
+    import bench_configs as bc
+
+    class R:
+        pass
+    rng = np.random.default_rng(1)
+    res, parts = [], []
+    for i in range(4):
+        r = R()
+        r.polished_len, r.n_cigar, r.rounds, r.substituted_bases, r.inserted_bases, r.deleted_bases, r.status = 5 + i, 1 + i, 4, i, 2 * i, 3, 0
+        res.append(r)
+        parts.append((None, rng.integers(0, 4, 20).astype(np.uint8), None, C.create_string_buffer(b"MDMIM" + b"\0" * 10, 16),
+                      rng.integers(1, 99, 16).astype(np.uint32)))
+    out = bc.unpack_shard(bc.pack_shard(dict(n=4, res=res, parts=parts)))
+    for i, (p, o, c, k) in enumerate(out):
+        assert np.array_equal(p, parts[i][1][:5 + i]) and bytes(o) == b"MDMIM"[:1 + i] and np.array_equal(c, parts[i][4][:1 + i])
+        assert list(k) == [4, i, 2 * i, 3]
+    assert bc.unpack_shard(bc.pack_shard(dict(n=0, res=[], parts=[]))) == []
