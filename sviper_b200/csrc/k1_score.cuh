@@ -69,8 +69,9 @@ struct K1Mix
 {
     const int32_t *n_dev;      // number of tasks (pairs if MIXED) of this launch, on the device; null: `ntasks`
     int32_t *sstate;           // per task: bit 0 strand known, bit 1 is_rc, bit 2 weak (winner scored < K1_WEAK: its certificate
-                               // would probably fail again), bits 3..12 the winner's last score (clamped to 0..1023; only used
-                               // to PREDICT the certificate, never to decide it), bits 16..31 bound on the other strand's score
+                               // would probably fail again), bits 3..12 the winner's last score (clamped to 0..1023) and
+                               // bit 13 "that score comes from a mixed round" (both only used to PREDICT the certificate,
+                               // never to decide it), bits 16..31 bound on the other strand's score
     const int32_t *emax;       // per window: edit cost E for W = 320, W = 512
     int32_t *fb19, *fb32;      // lists the failed certificates are appended to (both strands again, same round)
     int32_t *fb_cnt;           // their counters [2]
@@ -303,7 +304,7 @@ __global__ void __launch_bounds__(THREADS, 512 / THREADS) k1_score_kernel(const 
                     o.col_f = rc ? 0 : col; o.col_r = rc ? col : 0;
                     out[t] = o;
                     mix.sstate[t] = (int32_t)(((uint32_t)nb << 16) | (uint32_t)(rc << 1) | 1u | (sc < K1_WEAK ? 4u : 0u) |
-                                              ((uint32_t)max(0, min(1023, sc)) << 3));
+                                              ((uint32_t)max(0, min(1023, sc)) << 3) | (1u << 13));
                 }
                 else
                 {
@@ -336,15 +337,17 @@ __global__ void mix_plan_kernel(const int32_t *__restrict__ pair_task, int64_t n
     const int R1 = read_len[task_read[t1]], R2 = t2 >= 0 ? read_len[task_read[t2]] : 0;
     const int s1 = sstate[t1], s2 = t2 >= 0 ? sstate[t2] : 0;
     // Will the certificate hold? The mixed launch accepts a read iff its new score S satisfies S >= 0 and S > max(bound + E, -6)
-    // (E = emax of its window). S is not known yet, but polishing rarely lowers a read's score, so a read whose LAST score (less
-    // a small margin) does not clear bound + E is expected to fail and goes to the regular list right away -- that list runs
-    // BESIDE the mixed launch, whereas a failure inside it costs another launch behind it. Only a prediction: a wrong guess
-    // either way changes where the read is aligned, never the result. (Predicting with last - E, the worst case, sent most
-    // reads of round 2 to the regular list: 2.29 vs 1.89 ms per step.)
+    // (E = emax of its window). S is not known yet. After a REGULAR round the last score was taken against the unpolished
+    // consensus and says little (the round's edits raise it by about what E charges for them): the read is tried. After a MIXED
+    // round the consensus is nearly final, so a read whose last score (less a small margin) does not clear bound + E is expected
+    // to fail and goes to the regular list right away -- that list runs BESIDE the mixed launch, whereas a failure inside it
+    // costs another launch behind it (142 us when few tasks are live). Only a prediction: a wrong guess either way changes
+    // where the read is aligned, never the result. (Measured: predicting after regular rounds too sends most reads of
+    // windows with many edits to the regular list, configs[3] 889 vs 1,015 variants/s.)
     auto shaky = [&](int st, int R) {
         const int e = emax[2 * task_win[t1] + (R > 152)];
         const int last = (st >> 3) & 1023, bound = st >> 16;
-        return (st & 4) || (last - 8) <= max(bound + e, -6);
+        return (st & 4) || (((st >> 13) & 1) && (last - 8) <= max(bound + e, -6));
     };
     if (t2 >= 0 && (s1 & 1) && (s2 & 1) && !shaky(s1, R1) && !shaky(s2, R2))
     {
