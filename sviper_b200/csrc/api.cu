@@ -11,7 +11,6 @@
 #include <deque>
 #include <cub/device/device_scan.cuh>
 #include <nvtx3/nvToolsExt.h>
-#include <sched.h>
 #include "ctx.cuh"
 #include "k1_score.cuh"
 
@@ -111,14 +110,8 @@ static svp_ctx *make_ctx(int cuda_device, void *cuda_stream, bool is_lane)
     }
     if (cudaHostAlloc((void **)&ctx->h_ctl, 2 * sizeof(svp::RoundCtl), cudaHostAllocDefault) != cudaSuccess) { delete ctx; return nullptr; }
     memset(ctx->h_ctl, 0, 2 * sizeof(svp::RoundCtl));
-    {
-        // blocking waits when this process has few cores for its lane threads (see svp_sync)
-        cpu_set_t set;
-        int cores = 64;
-        if (sched_getaffinity(0, sizeof set, &set) == 0) cores = CPU_COUNT(&set);
-        ctx->blocking_sync = cores < 3 * SVP_DEFAULT_LANES;
-        if (const char *bs = getenv("SVP_BLOCKING_SYNC")) ctx->blocking_sync = atoi(bs) == 1;
-    }
+    // spinning waits by default; SVP_BLOCKING_SYNC=1 makes the waits sleep (see svp_sync for the measurement)
+    if (const char *bs = getenv("SVP_BLOCKING_SYNC")) ctx->blocking_sync = atoi(bs) == 1;
     const unsigned evf = cudaEventDisableTiming | (ctx->blocking_sync ? cudaEventBlockingSync : 0);
     cudaEventCreateWithFlags(&ctx->ev_sync, evf);
     for (int i = 0; i < 2; ++i) cudaEventCreateWithFlags(&ctx->ev_ctl[i], evf);

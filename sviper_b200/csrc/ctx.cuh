@@ -159,7 +159,7 @@ struct svp_ctx
     svp::RoundCtl *h_ctl = nullptr;          // pinned, 2 slots
     cudaEvent_t ev_ctl[2] = {nullptr, nullptr};
     int64_t cap_units = 0, cap_words = 0;   // what the per-round arenas (records, paths, trace) currently hold
-    bool blocking_sync = false;             // svp_sync: sleep instead of spin (SVP_BLOCKING_SYNC=0|1; default by core count)
+    bool blocking_sync = false;             // svp_sync: sleep instead of spin (SVP_BLOCKING_SYNC=1)
     cudaEvent_t ev_sync = nullptr;
     int n_regrow = 0;                       // rounds repeated because an arena had to grow
     bool sync_rounds = true;                // wait for the outcome of a round before queueing the next (SVP_SPECULATIVE_ROUNDS=1: one round ahead)
@@ -170,10 +170,11 @@ struct svp_ctx
     struct MsaSession *msa = nullptr;
 };
 
-// Waits for everything queued on the context's stream. On a host with few cores per GPU (8 ranks x 4 lane threads on 32
-// cores) the default spinning wait of the CUDA runtime lets the lane threads starve each other and the submitting thread;
-// there the wait goes through an event created with cudaEventBlockingSync (the thread sleeps). With cores to spare the
-// spinning wait is kept: it returns ~20 us sooner, several times per round.
+// Waits for everything queued on the context's stream: the CUDA runtime's spinning wait. SVP_BLOCKING_SYNC=1 waits on an event
+// created with cudaEventBlockingSync instead (the thread sleeps). Measured on an 8-GPU box with every rank pinned to its
+// 4-core slice (4 lane threads + the submitting thread per rank), where sleeping waits looked attractive: they cost 2.8x
+// (38,654 vs 109,913 variants/s at N = 8) -- a round ends with a wait, and every wake-up adds tens of microseconds to a
+// ~0.5 ms round. Spinning stays the default.
 static inline cudaError_t svp_sync(svp_ctx *ctx)
 {
     if (!ctx->blocking_sync) return cudaStreamSynchronize(ctx->stream);
