@@ -334,13 +334,30 @@ def run_whole_program(n_records, cores, local_gpu):
         t0 = time.perf_counter()
         subprocess.check_call([ref_bin] + base + ["-o", os.path.join(tmp, "ref")], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
         t_ref = time.perf_counter() - t0
-        same = open(os.path.join(tmp, "gpu.vcf")).read() == open(os.path.join(tmp, "ref.vcf")).read()
-        rows = [x.split("\t") for x in open(os.path.join(tmp, "ref.vcf")) if not x.startswith("#")]
+        recs = lambda path: [x for x in open(path) if not x.startswith("#")]
+        gpu_rows = recs(os.path.join(tmp, "gpu.vcf"))
+        ref_runs = [recs(os.path.join(tmp, "ref.vcf"))]
+        same = gpu_rows == ref_runs[0]
+        # The reference is not run-to-run deterministic with several threads (profiles/r2_reference_determinism.txt: which long
+        # reads its BAM reader returns varies, so the consensus that goes into polishing varies for a few records). If the VCFs
+        # differ, the reference is run again (up to twice): the GPU program has to agree with ONE of its runs, and the records
+        # it differs on have to be records the reference disagrees with itself on.
+        while not any(gpu_rows == r for r in ref_runs) and len(ref_runs) < 3:
+            subprocess.check_call([ref_bin] + base + ["-o", os.path.join(tmp, "ref%d" % len(ref_runs))], stdout=subprocess.DEVNULL,
+                                  stderr=subprocess.DEVNULL)
+            ref_runs.append(recs(os.path.join(tmp, "ref%d.vcf" % len(ref_runs))))
+        differing = [i for i, (a, b) in enumerate(zip(gpu_rows, ref_runs[0])) if a != b]
+        unstable = [i for i in range(len(ref_runs[0])) if len({r[i] for r in ref_runs}) > 1]
+        determinism = {"records_differing_from_first_reference_run": len(differing), "reference_runs": len(ref_runs),
+                       "records_the_reference_runs_disagree_on": len(unstable),
+                       "vcf_identical_to_a_reference_run": any(gpu_rows == r for r in ref_runs),
+                       "every_differing_record_has_a_reference_run_with_the_same_line":
+                           all(any(gpu_rows[i] == r[i] for r in ref_runs) for i in differing)}
         return {"workload": "configs[1] shape as files: %d DELs of 50-1000 bp on a %d bp contig, 30x 2x150 bp + 20x long reads at "
                             "10%% error, -k 400, -t %d; FASTA/BAM/VCF written by tests/e2e_dataset.py" % (n_records, d["contig_len"], cores),
                 "reference_seconds": t_ref, "gpu_program_seconds": t_gpu, "speedup": t_ref / t_gpu,
                 "reference_variants_per_s": n_records / t_ref, "gpu_program_variants_per_s": n_records / t_gpu,
-                "vcf_identical": same, "records": len(rows), "pass_records": sum(r[6] == "PASS" for r in rows), "host_threads": cores,
+                "vcf_identical": same, "determinism": determinism, "records": len(rows), "pass_records": sum(r[6] == "PASS" for r in rows), "host_threads": cores,
                 "mean_device_batch": float(stats.get("mean_device_batch", 0)), "device_batches": int(stats.get("device_batches", 0)),
                 "peak_parked_variants_per_thread": int(stats.get("peak_parked_per_thread", 0)),
                 "gpu_busy_percent_mean": busy.mean(), "gpu_busy_percent_max": busy.peak(), "dataset_seconds": t_gen,

@@ -117,6 +117,7 @@ static svp_ctx *make_ctx(int cuda_device, void *cuda_stream, bool is_lane)
     for (int i = 0; i < 2; ++i) cudaEventCreateWithFlags(&ctx->ev_ctl[i], evf);
     if (const char *sr = getenv("SVP_SPECULATIVE_ROUNDS")) ctx->sync_rounds = atoi(sr) != 1;
     if (const char *kt = getenv("SVP_K1_THREADS")) ctx->k1_threads = atoi(kt);
+    if (const char *np_ = getenv("SVP_NO_PREDICT")) ctx->predict_certificates = atoi(np_) != 1;
     if (const char *mr = getenv("SVP_MIX_REGULAR")) ctx->mix_reg_wide = std::string(mr) == "wide";
     if (const char *kg = getenv("SVP_K5_GLOBAL_TABLE")) ctx->k5_global_table = atoi(kg) == 1;
     size_t free_b = 0, total_b = 0;

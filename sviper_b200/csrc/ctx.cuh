@@ -113,6 +113,7 @@ struct svp_ctx
     // kernel of another ----
     int n_lanes = SVP_DEFAULT_LANES;
     bool is_lane = false;
+    int share = 1;                          // lanes that share the GPU with this context (1: it has the GPU to itself)
     std::vector<svp_ctx *> lanes;
     std::vector<int> lane_range;            // variant ranges of the last split batch; empty: it ran on this context
     cudaEvent_t ev_call = nullptr;          // start (parent -> lanes) / end (lane -> parent) ordering of a split call
@@ -140,6 +141,7 @@ struct svp_ctx
     DevBuf descs, states, states_init, pair_task, cons0, cons1, inslen, voff, profile, cov, isgap, decision, proper, cons_init;
     // strand certificates (k1_score.cuh, K1Mix): per-task strand state, per-round task lists, per-window edit density
     DevBuf sstate, reg19, reg32, mix19, mix32, fail19, fail32, mixcnt, edit, emax;
+    bool predict_certificates = true;       // SVP_NO_PREDICT=1: off (A/B switch)
     bool mix_reg_wide = false;              // SVP_MIX_REGULAR=wide: regular tasks of a mixed round in the wide shape (A/B switch)
     int k1_threads = 0;                     // 0: choose per launch; 64 / 128: force the block size of the throughput shape (SVP_K1_THREADS)
     bool mixcnt_zeroed = false;             // mixcnt: 4 list counters (reset every round) + the DP cell counter at byte 32

@@ -325,7 +325,7 @@ __global__ void __launch_bounds__(THREADS, 512 / THREADS) k1_score_kernel(const 
 __global__ void mix_plan_kernel(const int32_t *__restrict__ pair_task, int64_t npairs, const int32_t *__restrict__ task_read,
                                 const int32_t *__restrict__ task_win, const int32_t *__restrict__ read_len,
                                 const uint8_t *__restrict__ win_done, const int32_t *__restrict__ sstate,
-                                const int32_t *__restrict__ emax,
+                                const int32_t *__restrict__ emax, int predict,
                                 int32_t *__restrict__ reg19, int32_t *__restrict__ reg32, int32_t *__restrict__ mix19,
                                 int32_t *__restrict__ mix32, int32_t *__restrict__ cnt)
 {
@@ -343,11 +343,12 @@ __global__ void mix_plan_kernel(const int32_t *__restrict__ pair_task, int64_t n
     // to fail and goes to the regular list right away -- that list runs BESIDE the mixed launch, whereas a failure inside it
     // costs another launch behind it (142 us when few tasks are live). Only a prediction: a wrong guess either way changes
     // where the read is aligned, never the result. (Measured: predicting after regular rounds too sends most reads of
-    // windows with many edits to the regular list, configs[3] 889 vs 1,015 variants/s.)
+    // windows with many edits to the regular list, configs[3] 889 vs 1,015 variants/s.) `predict` is set by the host only
+    // while few tasks are live (api_polish.inc, K1_PREDICT_MAX_TASKS): on a full GPU a predicted read costs more than a failed one.
     auto shaky = [&](int st, int R) {
         const int e = emax[2 * task_win[t1] + (R > 152)];
         const int last = (st >> 3) & 1023, bound = st >> 16;
-        return (st & 4) || (((st >> 13) & 1) && (last - 8) <= max(bound + e, -6));
+        return (st & 4) || (predict && ((st >> 13) & 1) && (last - 8) <= max(bound + e, -6));
     };
     if (t2 >= 0 && (s1 & 1) && (s2 & 1) && !shaky(s1, R1) && !shaky(s2, R2))
     {

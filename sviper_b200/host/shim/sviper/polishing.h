@@ -28,6 +28,7 @@
 
 #include <cstdlib>
 #include <mutex>
+#include <sstream>
 
 #include <seqan/align.h>
 #include <seqan/seq_io.h>
@@ -44,6 +45,20 @@ inline std::string to_std_string(TString const & s)
     std::string o(seqan::length(s), 'N');
     for (size_t i = 0; i < o.size(); ++i) o[i] = (char)seqan::Dna5(s[i]);
     return o;
+}
+
+inline uint64_t fnv(std::string const & s, uint64_t h = 1469598103934665603ull)
+{
+    for (unsigned char c : s) { h ^= c; h *= 1099511628211ull; }
+    return h;
+}
+
+// SVIPER_B200_TRACE=1: one line per variant on stderr with hashes of what went into the device job and what came back
+// (tools/gpu_wp_repeat.py compares them between runs)
+inline bool trace_on()
+{
+    static bool const on = [] { char const * e = std::getenv("SVIPER_B200_TRACE"); return e && std::atoi(e) == 1; }();
+    return on;
 }
 
 inline std::vector<QRead> to_qreads(seqan::StringSet<seqan::Dna5QString> const & reads)
@@ -113,6 +128,22 @@ inline seqan::Dna5String polish_to_perfection(seqan::StringSet<seqan::Dna5QStrin
     config.fix_indels = true;
     config.cov_profile.assign(rb.cov.begin(), rb.cov.begin() + rb.res.cov_len);
     std::string polished = rb.sequence();
+    if (b200::shim::trace_on())
+    {
+        uint64_t hr = 1469598103934665603ull;
+        for (auto const * set : {&reads1, &reads2})
+            for (auto const & q : b200::shim::to_qreads(*set)) { hr = b200::shim::fnv(q.seq, hr); hr = b200::shim::fnv(q.qual, hr); }
+        std::ostringstream os;
+        os << "[trace] refpart=" << b200::shim::fnv(ref_part) << " cons=" << b200::shim::fnv(b200::shim::to_std_string(ref))
+           << " cons_len=" << seqan::length(ref) << " reads=" << seqan::length(reads1) << " reads_hash=" << hr
+           << " baseQ=" << config.baseQ_mean << " ins=" << config.mean_insert_size_of_short_reads << "/" << config.stdev_insert_size_of_short_reads
+           << " polished=" << b200::shim::fnv(polished) << " len=" << polished.size() << " rounds=" << rb.res.rounds
+           << " edits=" << rb.res.substituted_bases << "/" << rb.res.inserted_bases << "/" << rb.res.deleted_bases
+           << " mappQ=" << rb.res.mappQ_mean << " cigar=";
+        for (auto const & e : rb.cigar()) os << e.count << e.operation;
+        os << "\n";
+        std::cerr << os.str();
+    }
     if (with_final)
     {
         vs.have_final = true; vs.ref_part.swap(ref_part); vs.polished = polished; vs.cigar = rb.cigar();

@@ -69,12 +69,15 @@ def rows_of(vcf_text):
 @pytest.mark.parametrize("seed", [1, 2])
 def test_vcf_identical_to_reference(tmp_path, seed):
     """The unmodified reference program against both GPU programs -- the unmodified src/sviper.cpp over the shims
-    (sviper_b200_cli) and the prepare / device / finish pipeline (sviper_b200) -- single- and multi-threaded: byte-identical
-    VCFs and identical hot-path log lines. (The reference is run with 8 threads: its output does not depend on the thread
-    count, profiles/r2_reference_determinism.txt.)"""
+    (sviper_b200_cli) and the prepare / device / finish pipeline (sviper_b200): byte-identical VCFs and identical hot-path
+    log lines. Single-threaded runs are compared with the reference's single-threaded run, strictly. With several threads the
+    REFERENCE ITSELF is not run-to-run deterministic (profiles/r2_reference_determinism.txt: the same binary on the same files
+    gave three different VCFs in seven multi-threaded runs -- which long reads its BAM reader returns varies, so the
+    consensus that goes INTO polishing varies; the GPU programs run that same host code). A multi-threaded GPU run therefore
+    has to equal SOME run of the reference: the single-threaded one, or one of up to three fresh multi-threaded ones."""
     assert os.path.exists(REF_BIN) and os.path.exists(GPU_BIN) and os.path.exists(PIPE_BIN), "build() must have produced the binaries"
     d = e2e_dataset.make(str(tmp_path), seed=seed)
-    ref_vcf = run(REF_BIN, d, str(tmp_path / "ref"), 8)
+    ref_vcf = run(REF_BIN, d, str(tmp_path / "ref"), 1)
     rows = rows_of(ref_vcf)
     assert len(rows) == d["n_records"]
     assert sum(r[6] == "PASS" for r in rows) >= 5
@@ -86,10 +89,23 @@ def test_vcf_identical_to_reference(tmp_path, seed):
     assert any(r[6] == "PASS" and r[4] == "<INS>" and svlen(r) >= 1000 and float(r[5]) > 50 for r in rows)
     a = hot_path_lines(str(tmp_path / "ref.log"))
     assert len(a) >= 30
-    for name, binary, threads in (("cli1", GPU_BIN, 1), ("cli4", GPU_BIN, 4), ("pipe1", PIPE_BIN, 1), ("pipe4", PIPE_BIN, 4)):
-        vcf = run(binary, d, str(tmp_path / name), threads)
+    for name, binary in (("cli1", GPU_BIN), ("pipe1", PIPE_BIN)):
+        vcf = run(binary, d, str(tmp_path / name), 1)
         assert vcf == ref_vcf, name
         assert hot_path_lines(str(tmp_path / (name + ".log"))) == a, name
+    refs = [(ref_vcf, a)]                       # every output the reference has produced for these files so far
+    for name, binary in (("cli4", GPU_BIN), ("pipe4", PIPE_BIN)):
+        for attempt in range(3):
+            vcf = run(binary, d, str(tmp_path / name), 4)
+            lines = hot_path_lines(str(tmp_path / (name + ".log")))
+            if any(vcf == rv and lines == rl for rv, rl in refs):
+                break
+            rv = run(REF_BIN, d, str(tmp_path / ("ref4_%s_%d" % (name, attempt))), 4)
+            refs.append((rv, hot_path_lines(str(tmp_path / ("ref4_%s_%d.log" % (name, attempt))))))
+            if any(vcf == rv and lines == rl for rv, rl in refs):
+                break
+        else:
+            raise AssertionError("%s: no multi-threaded run matched any of %d reference outputs" % (name, len(refs)))
 
 
 @pytest.mark.gpu
@@ -99,7 +115,7 @@ def test_pipeline_parks_variants_and_batches_them(tmp_path):
     (the device is far faster than one host thread prepares); SVP_BATCH_TARGET + SVP_LINGER_MS keep the lanes back until
     several variants wait, so here they are polished as shared device batches. The VCF does not change."""
     d = e2e_dataset.make(str(tmp_path), seed=7, contig_len=100000)
-    ref_vcf = run(REF_BIN, d, str(tmp_path / "ref"), 8)
+    ref_vcf = run(REF_BIN, d, str(tmp_path / "ref"), 1)
     env = dict(os.environ, SVIPER_B200_STATS="1", SVP_BATCH_TARGET="6", SVP_LINGER_MS="20000")
     p = subprocess.run([PIPE_BIN, "-c", d["vcf"], "-l", d["long"], "-s", d["short"], "-r", d["ref"], "-k", str(d["k"]),
                         "-o", str(tmp_path / "pipe"), "-t", "1"], stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True, env=env)
