@@ -133,38 +133,101 @@ class GpuBusySampler(threading.Thread):
         return float(np.max(self.vals)) if self.vals else None
 
 
+def _result_fields(res, n, names):
+    """int32 fields of a ctypes array of svp_result structs as numpy columns (one strided view per field, no per-record
+    Python objects); falls back to attribute access for plain objects (tests)."""
+    import ctypes as C
+    if n and isinstance(res, C.Array):
+        raw = np.frombuffer(res, np.uint8, n * C.sizeof(res._type_)).reshape(n, C.sizeof(res._type_))
+        return [raw[:, getattr(res._type_, f).offset:getattr(res._type_, f).offset + 4].copy().view(np.int32).ravel() for f in names]
+    return [np.fromiter((getattr(res[i], f) for i in range(n)), np.int32, n) for f in names]
+
+
 def pack_shard(pb):
-    """What a rank hands to the gather, straight from the caller-side result buffers of a prepared batch (no per-variant
-    Python objects): one uint8 array = header | polished lengths | CIGAR lengths | counters | polished bases | CIGAR ops |
-    CIGAR counts."""
+    """What a rank hands to the gather, straight from the caller-side result buffers of a prepared batch: one uint8 array =
+    header | polished lengths | CIGAR lengths | counters | polished bases | CIGAR ops | CIGAR counts."""
     n = pb["n"]
-    res = pb["res"]
-    plen = np.fromiter((res[i].polished_len for i in range(n)), np.int32, n)
-    ncig = np.fromiter((res[i].n_cigar for i in range(n)), np.int32, n)
-    cnt4 = np.fromiter((x for i in range(n) for x in (res[i].rounds, res[i].substituted_bases, res[i].inserted_bases,
-                                                      res[i].deleted_bases)), np.int32, 4 * n)
-    if any(res[i].status != 0 for i in range(n)):
+    status, plen, ncig, rounds, sub, ins, dele = _result_fields(pb["res"], n, ("status", "polished_len", "n_cigar", "rounds",
+                                                                           "substituted_bases", "inserted_bases", "deleted_bases"))
+    if np.any(status != 0):
         raise RuntimeError("a variant of the shard failed")
-    pol = np.concatenate([pb["parts"][i][1][:plen[i]] for i in range(n)]) if n else np.zeros(0, np.uint8)
-    ops = np.concatenate([np.frombuffer(pb["parts"][i][3], np.uint8, int(ncig[i])) for i in range(n)]) if n else np.zeros(0, np.uint8)
-    cnts = np.concatenate([pb["parts"][i][4][:ncig[i]] for i in range(n)]) if n else np.zeros(0, np.uint32)
+    cnt4 = np.stack([rounds, sub, ins, dele], axis=1).astype(np.int32).ravel() if n else np.zeros(0, np.int32)
+    parts = pb["parts"]
+    pol = np.concatenate([parts[i][1][:plen[i]] for i in range(n)]) if n else np.zeros(0, np.uint8)
+    ops = np.concatenate([np.frombuffer(parts[i][3], np.uint8, int(ncig[i])) for i in range(n)]) if n else np.zeros(0, np.uint8)
+    cnts = np.concatenate([parts[i][4][:ncig[i]] for i in range(n)]) if n else np.zeros(0, np.uint32)
     head = np.array([n, len(pol), len(ops)], np.int64)
     return np.concatenate([head.view(np.uint8), plen.view(np.uint8), ncig.view(np.uint8), cnt4.view(np.uint8), pol, ops,
                            cnts.astype(np.uint32).view(np.uint8)])
 
 
+class Shard:
+    """a packed shard, unpacked as views (structure of arrays): record i = (polished bases, CIGAR ops, CIGAR counts, counters)"""
+
+    def __init__(self, buf):
+        n, npol, nops = (int(x) for x in buf[:24].view(np.int64))
+        o = 24
+        self.n = n
+        self.plen = buf[o:o + 4 * n].view(np.int32); o += 4 * n
+        self.ncig = buf[o:o + 4 * n].view(np.int32); o += 4 * n
+        self.cnt4 = buf[o:o + 16 * n].view(np.int32).reshape(n, 4); o += 16 * n
+        self.pol = buf[o:o + npol]; o += npol
+        self.ops = buf[o:o + nops]; o += nops
+        self.cnts = buf[o:o + 4 * nops].view(np.uint32)
+        self.pe, self.ce = np.cumsum(self.plen, dtype=np.int64), np.cumsum(self.ncig, dtype=np.int64)
+
+    def record(self, i):
+        pe, ce, pl, nc = self.pe[i], self.ce[i], self.plen[i], self.ncig[i]
+        return self.pol[pe - pl:pe], self.ops[ce - nc:ce], self.cnts[ce - nc:ce], self.cnt4[i]
+
+
 def unpack_shard(buf):
     """-> list of (polished bases, CIGAR ops, CIGAR counts, (rounds, subst, ins, del)) views, in shard order"""
-    n, npol, nops = (int(x) for x in buf[:24].view(np.int64))
-    o = 24
-    plen = buf[o:o + 4 * n].view(np.int32); o += 4 * n
-    ncig = buf[o:o + 4 * n].view(np.int32); o += 4 * n
-    cnt4 = buf[o:o + 16 * n].view(np.int32).reshape(n, 4); o += 16 * n
-    pol = buf[o:o + npol]; o += npol
-    ops = buf[o:o + nops]; o += nops
-    cnts = buf[o:o + 4 * nops].view(np.uint32)
-    pe, ce = np.cumsum(plen), np.cumsum(ncig)
-    return [(pol[pe[i] - plen[i]:pe[i]], ops[ce[i] - ncig[i]:ce[i]], cnts[ce[i] - ncig[i]:ce[i]], cnt4[i]) for i in range(n)]
+    sh = Shard(buf)
+    return [sh.record(i) for i in range(sh.n)]
+
+
+class LocalResults:
+    """world size 1: nothing to gather, the result buffers of the call are already in input order"""
+
+    def __init__(self, pb):
+        self.pb = pb
+        status, self.plen, self.ncig = _result_fields(pb["res"], pb["n"], ("status", "polished_len", "n_cigar"))
+        if np.any(status != 0):
+            raise RuntimeError("a variant of the shard failed")
+
+    def __len__(self):
+        return self.pb["n"]
+
+    def record(self, j):
+        r, part = self.pb["res"][j], self.pb["parts"][j]
+        return (part[1][:self.plen[j]], np.frombuffer(part[3], np.uint8, int(self.ncig[j])), part[4][:self.ncig[j]],
+                (r.rounds, r.substituted_bases, r.inserted_bases, r.deleted_bases))
+
+
+class GatheredResults:
+    """The shards of all ranks on the host of rank 0 with an index in INPUT order (the reference writes its VCF from one vector
+    in input order, io.h:89-90): record j of the candidate list = shard rank_of[j], position local_of[j]. Built with array
+    operations only -- 5,000 per-record Python objects cost more than a rank's whole device time at 8 GPUs."""
+
+    def __init__(self, n_total, owners, bufs):
+        self.shards = [Shard(b) for b in bufs]
+        self.rank_of = np.full(n_total, -1, np.int32)
+        self.local_of = np.zeros(n_total, np.int32)
+        for r, (own, sh) in enumerate(zip(owners, self.shards)):
+            own = np.asarray(own, np.int64)
+            if len(own) != sh.n:
+                raise ValueError("rank %d returned %d results for %d records" % (r, sh.n, len(own)))
+            self.rank_of[own] = r
+            self.local_of[own] = np.arange(len(own), dtype=np.int32)
+        if np.any(self.rank_of < 0):
+            raise ValueError("records without a result")
+
+    def __len__(self):
+        return len(self.rank_of)
+
+    def record(self, j):
+        return self.shards[self.rank_of[j]].record(self.local_of[j])
 
 
 def run_sharded_c3(ctx, rank, world, flush, gloo, n_total, shard, t_gen, barrier, max_over_ranks, sum_over_ranks):
@@ -186,27 +249,23 @@ def run_sharded_c3(ctx, rank, world, flush, gloo, n_total, shard, t_gen, barrier
         flush.zero_(); torch.cuda.synchronize()
         barrier(world)
         t0 = time.perf_counter()
-        ctx.run_prepared(pb)                               # host buffers -> device -> host buffers, 4 lanes
+        # host buffers -> device -> host buffers, 4 lanes, one blocking call for the shard (queueing the shard variant by
+        # variant through the asynchronous scheduler measured the same: 306 vs 313 ms for 5,000 records, 40.0 vs 39.9 ms for 625)
+        ctx.run_prepared(pb)
         t_dev = time.perf_counter() - t0
-        mine = torch.from_numpy(pack_shard(pb))
         if world > 1:
             # host gather to rank 0 (gloo): sizes first, then the byte arrays as padded uint8 tensors
+            mine = torch.from_numpy(pack_shard(pb))
             sizes = [torch.zeros(1, dtype=torch.int64) for _ in range(world)]
             dist.all_gather(sizes, torch.tensor([mine.numel()], dtype=torch.int64), group=gloo)
             cap = int(max(int(x) for x in sizes))
             padded = torch.zeros(cap, dtype=torch.uint8); padded[:mine.numel()] = mine
             bufs = [torch.zeros(cap, dtype=torch.uint8) for _ in range(world)] if rank == 0 else None
             dist.gather(padded, bufs, dst=0, group=gloo)
-            parts = [b[:int(n)].numpy() for b, n in zip(bufs, sizes)] if rank == 0 else None
+            if rank == 0:
+                gathered = GatheredResults(n_total, owners, [b[:int(n)].numpy() for b, n in zip(bufs, sizes)])      # input order
         else:
-            parts = [mine.numpy()]
-        if rank == 0:
-            out = [None] * n_total
-            for r, part in enumerate(parts):
-                for j, item in zip(owners[r], unpack_shard(part)):
-                    out[j] = item                      # input order
-            assert all(x is not None for x in out)
-            gathered = out
+            gathered = LocalResults(pb)       # one rank: the caller's result buffers ARE the input-ordered vector
         times.append((time.perf_counter() - t0, t_dev))
     e2e_s = max_over_ranks(min(t[0] for t in times), world)
     # HBM-resident passes (every round + final alignment from resident inputs), device events
@@ -221,13 +280,20 @@ def run_sharded_c3(ctx, rank, world, flush, gloo, n_total, shard, t_gen, barrier
     tot_cells = sum_over_ranks(algorithmic_cells(shard, res), world)
     if rank != 0:
         return None
+    # (outside the timed region) what was gathered is what this rank's library call returned, record by record
+    for local, j in enumerate(owners[0]):
+        pol, ops, cnts, k4 = gathered.record(j)
+        r = res[local]
+        assert np.array_equal(pol, r["polished"]) and list(k4) == [r["rounds"], r["subst"], r["ins"], r["dele"]]
+        assert [(chr(o), int(c)) for o, c in zip(ops, cnts)] == r.get("cigar", [])
     return {"workload": "BASELINE.json configs[2]: one candidate list of %d mixed DEL/INS (50-1000 bp, 30x 2x150 bp, -k 400), "
                         "dealt to the ranks in order of decreasing estimated work (snake), results gathered on the host of rank 0 into "
                         "input order" % n_total,
             "scaling": "strong", "variants": n_total, "n_gpus": world,
             "e2e_variants_per_s": n_total / e2e_s, "e2e_seconds": e2e_s,
-            "e2e_includes": "staging + H2D + all kernels + D2H per rank, packing the shard's results into one byte array, gloo "
-                            "gather to rank 0, reordering into input order",
+            "e2e_includes": "staging + H2D + all kernels + D2H per rank; N > 1: packing the shard's results into one byte array, "
+                            "gloo gather to rank 0, input-order index over the gathered arrays (N = 1: the call's result buffers "
+                            "are already the input-ordered vector)",
             "gather_seconds_rank0": times[-1][0] - times[-1][1],
             "resident_variants_per_s": n_total / (max(all_ms) * 1e-3), "resident_ms_per_rank": all_ms,
             "rank_imbalance_max_over_mean": max(all_ms) / (sum(all_ms) / len(all_ms)),

@@ -47,3 +47,30 @@ def test_shard_packing_round_trip():
         assert np.array_equal(p, parts[i][1][:5 + i]) and bytes(o) == b"MDMIM"[:1 + i] and np.array_equal(c, parts[i][4][:1 + i])
         assert list(k) == [4, i, 2 * i, 3]
     assert bc.unpack_shard(bc.pack_shard(dict(n=0, res=[], parts=[]))) == []
+
+
+def test_shard_packing_reads_the_c_structs_and_gathers_in_input_order():
+    import bench_configs as bc
+    from sviper_b200 import api
+    rng = np.random.default_rng(2)
+    owners = [[0, 3, 4], [1, 2]]
+    bufs, want = [], {}
+    for own in owners:
+        n = len(own)
+        res = (api.Result * n)()
+        parts = []
+        for i, j in enumerate(own):
+            res[i].status = 0; res[i].polished_len = 7 + j; res[i].n_cigar = 1 + j % 3; res[i].rounds = 3 + j
+            res[i].substituted_bases = j; res[i].inserted_bases = 2 * j; res[i].deleted_bases = 5
+            parts.append((None, rng.integers(0, 4, 32).astype(np.uint8), None, C.create_string_buffer(b"MIDMI" + b"\0" * 10, 16),
+                          rng.integers(1, 99, 16).astype(np.uint32)))
+            want[j] = (parts[-1][1][:7 + j].copy(), b"MIDMI"[:1 + j % 3], parts[-1][4][:1 + j % 3].copy(), [3 + j, j, 2 * j, 5])
+        bufs.append(bc.pack_shard(dict(n=n, res=res, parts=parts)))
+    g = bc.GatheredResults(5, owners, bufs)
+    assert len(g) == 5
+    for j in range(5):
+        pol, ops, cnts, k4 = g.record(j)
+        assert np.array_equal(pol, want[j][0]) and bytes(ops) == want[j][1] and np.array_equal(cnts, want[j][2]) and list(k4) == want[j][3]
+    import pytest
+    with pytest.raises(ValueError):
+        bc.GatheredResults(6, owners, bufs)
