@@ -412,6 +412,7 @@ def run_whole_program(n_records, cores, local_gpu):
             subprocess.check_call([ref_bin] + base + ["-o", os.path.join(tmp, "ref%d" % len(ref_runs))], stdout=subprocess.DEVNULL,
                                   stderr=subprocess.DEVNULL)
             ref_runs.append(recs(os.path.join(tmp, "ref%d.vcf" % len(ref_runs))))
+        rows = [x.split("\t") for x in ref_runs[0]]
         differing = [i for i, (a, b) in enumerate(zip(gpu_rows, ref_runs[0])) if a != b]
         unstable = [i for i in range(len(ref_runs[0])) if len({r[i] for r in ref_runs}) > 1]
         determinism = {"records_differing_from_first_reference_run": len(differing), "reference_runs": len(ref_runs),

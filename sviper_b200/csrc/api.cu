@@ -110,9 +110,10 @@ static svp_ctx *make_ctx(int cuda_device, void *cuda_stream, bool is_lane)
     }
     if (cudaHostAlloc((void **)&ctx->h_ctl, 2 * sizeof(svp::RoundCtl), cudaHostAllocDefault) != cudaSuccess) { delete ctx; return nullptr; }
     memset(ctx->h_ctl, 0, 2 * sizeof(svp::RoundCtl));
-    // spinning waits by default; SVP_BLOCKING_SYNC=1 makes the waits sleep (see svp_sync for the measurement)
-    if (const char *bs = getenv("SVP_BLOCKING_SYNC")) ctx->blocking_sync = atoi(bs) == 1;
-    const unsigned evf = cudaEventDisableTiming | (ctx->blocking_sync ? cudaEventBlockingSync : 0);
+    // how host threads wait for the device (svp_wait_event, ctx.cuh)
+    if (const char *sm = getenv("SVP_SYNC"))
+        ctx->sync_mode = !strcmp(sm, "spin") ? SVP_SYNC_SPIN : !strcmp(sm, "block") ? SVP_SYNC_BLOCK : SVP_SYNC_YIELD;
+    const unsigned evf = cudaEventDisableTiming | (ctx->sync_mode == SVP_SYNC_BLOCK ? cudaEventBlockingSync : 0);
     cudaEventCreateWithFlags(&ctx->ev_sync, evf);
     for (int i = 0; i < 2; ++i) cudaEventCreateWithFlags(&ctx->ev_ctl[i], evf);
     if (const char *sr = getenv("SVP_SPECULATIVE_ROUNDS")) ctx->sync_rounds = atoi(sr) != 1;

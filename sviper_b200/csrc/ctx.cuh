@@ -1,5 +1,6 @@
 // Host-side context, growable device buffers and small utility kernels.
 #pragma once
+#include <sched.h>
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -99,6 +100,8 @@ struct MsaSession;
 
 constexpr int SVP_DEFAULT_LANES = 4, SVP_MAX_LANES = 16, SVP_MIN_PER_LANE = 4;
 
+enum { SVP_SYNC_YIELD = 0, SVP_SYNC_SPIN = 1, SVP_SYNC_BLOCK = 2 };
+
 struct svp_ctx
 {
     int device = 0;
@@ -161,7 +164,7 @@ struct svp_ctx
     svp::RoundCtl *h_ctl = nullptr;          // pinned, 2 slots
     cudaEvent_t ev_ctl[2] = {nullptr, nullptr};
     int64_t cap_units = 0, cap_words = 0;   // what the per-round arenas (records, paths, trace) currently hold
-    bool blocking_sync = false;             // svp_sync: sleep instead of spin (SVP_BLOCKING_SYNC=1)
+    int sync_mode = 0;                      // SVP_SYNC_* (svp_wait_event)
     cudaEvent_t ev_sync = nullptr;
     int n_regrow = 0;                       // rounds repeated because an arena had to grow
     bool sync_rounds = true;                // wait for the outcome of a round before queueing the next (SVP_SPECULATIVE_ROUNDS=1: one round ahead)
@@ -172,17 +175,32 @@ struct svp_ctx
     struct MsaSession *msa = nullptr;
 };
 
-// Waits for everything queued on the context's stream: the CUDA runtime's spinning wait. SVP_BLOCKING_SYNC=1 waits on an event
-// created with cudaEventBlockingSync instead (the thread sleeps). Measured on an 8-GPU box with every rank pinned to its
-// 4-core slice (4 lane threads + the submitting thread per rank), where sleeping waits looked attractive: they cost 2.8x
-// (38,654 vs 109,913 variants/s at N = 8) -- a round ends with a wait, and every wake-up adds tens of microseconds to a
-// ~0.5 ms round. Spinning stays the default.
+// Host waits. Three ways (SVP_SYNC=yield|spin|block, default yield):
+//   spin   the CUDA runtime's spinning wait (cudaStreamSynchronize / cudaEventSynchronize)
+//   yield  polls the event and calls sched_yield() between polls: as prompt as spinning while cores are free, but a waiting
+//          thread gives its core away when more threads than cores are runnable -- the case on an 8-GPU box, where a rank has
+//          a 4-core slice for 4 lane threads + the submitting thread (pure spinning there: 151 k variants/s end to end in one
+//          run, 102 k in the next, depending on which thread the scheduler starved)
+//   block  waits on an event created with cudaEventBlockingSync (the thread sleeps): 2.8x slower at N = 8 (38,654 vs 109,913
+//          variants/s) -- a round ends with a wait, and every wake-up adds tens of microseconds to a ~0.5 ms round
+static inline cudaError_t svp_wait_event(svp_ctx *ctx, cudaEvent_t ev)
+{
+    if (ctx->sync_mode != SVP_SYNC_YIELD) return cudaEventSynchronize(ev);
+    for (;;)
+    {
+        const cudaError_t e = cudaEventQuery(ev);
+        if (e != cudaErrorNotReady) return e;
+        sched_yield();
+    }
+}
+
+// waits for everything queued on the context's stream
 static inline cudaError_t svp_sync(svp_ctx *ctx)
 {
-    if (!ctx->blocking_sync) return cudaStreamSynchronize(ctx->stream);
+    if (ctx->sync_mode == SVP_SYNC_SPIN) return cudaStreamSynchronize(ctx->stream);
     cudaError_t e = cudaEventRecord(ctx->ev_sync, ctx->stream);
     if (e != cudaSuccess) return e;
-    return cudaEventSynchronize(ctx->ev_sync);
+    return svp_wait_event(ctx, ctx->ev_sync);
 }
 
 static int svp_fail(svp_ctx *ctx, cudaError_t e, const char *what, const char *file, int line)

@@ -74,3 +74,30 @@ def test_shard_packing_reads_the_c_structs_and_gathers_in_input_order():
     import pytest
     with pytest.raises(ValueError):
         bc.GatheredResults(6, owners, bufs)
+
+
+def test_whole_program_comparison_logic(tmp_path, monkeypatch):
+    """bench.py's whole_program key with the reference binary standing in for the GPU program (no GPU here): identical VCFs
+    are reported as such; a perturbed record makes it rerun the reference and report that no reference run has that line."""
+    import os
+    import pytest
+    import bench_configs as bc
+    ref = os.path.join(bc.ROOT, "oracle", "_ref", "sviper")
+    if not os.path.exists(ref):
+        pytest.skip("oracle/_ref/sviper not built")
+    root = tmp_path / "root"
+    (root / "oracle" / "_ref").mkdir(parents=True)
+    (root / "sviper_b200" / "host").mkdir(parents=True)
+    os.symlink(ref, str(root / "oracle" / "_ref" / "sviper"))
+    stand_in = root / "sviper_b200" / "host" / "sviper_b200"
+    stand_in.write_text('#!/bin/bash\n%s "$@" || exit 1\nout=""; while [ $# -gt 0 ]; do if [ "$1" = "-o" ]; then out=$2; fi; shift; done\n'
+                        'if [ -n "$PERTURB" ]; then sed -i \'0,/\\t9[0-9.]*\\tPASS/s/\\t9[0-9.]*\\tPASS/\\t12.5\\tPASS/\' $out.vcf; fi\n' % ref)
+    stand_in.chmod(0o755)
+    monkeypatch.setattr(bc, "ROOT", str(root))
+    r = bc.run_whole_program(2, 4, 0)
+    assert r["vcf_identical"] and r["determinism"]["reference_runs"] == 1 and r["pass_records"] == 2 and r["records"] == 7
+    monkeypatch.setenv("PERTURB", "1")
+    r = bc.run_whole_program(2, 4, 0)
+    d = r["determinism"]
+    assert not r["vcf_identical"] and d["reference_runs"] == 3 and d["records_differing_from_first_reference_run"] == 1
+    assert not d["vcf_identical_to_a_reference_run"] and not d["every_differing_record_has_a_reference_run_with_the_same_line"]

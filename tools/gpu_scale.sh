@@ -1,7 +1,12 @@
 #!/bin/bash
-# Runs on an 8-GPU box (gpurun --gpus 8 -- bash tools/gpu_scale.sh): bench.py at N = 1, 2, 4, 8 the way the driver launches it.
-python bench.py --gpus 1 --steps 20 --warmup 3 --c4-variants 0 --no-c5-full --whole-program-records 0 > gpurun_out/r2_scale_n1.json 2> gpurun_out/r2_scale_n1.err
-for n in 2 4 8; do
+# Runs on an 8-GPU box (gpurun --gpus 8 -- bash tools/gpu_scale.sh [N ...]): bench.py at N = 1, 2, 4, 8 (or the listed N) the way
+# the driver launches it.
+NS=${@:-1 2 4 8}
+for n in $NS; do
+  if [ $n = 1 ]; then
+    python bench.py --gpus 1 --steps 20 --warmup 3 --c4-variants 0 --no-c5-full --whole-program-records 0 > gpurun_out/r2_scale_n1.json 2> gpurun_out/r2_scale_n1.err
+    continue
+  fi
   python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $((29500 + n)) bench.py --gpus $n --steps 20 --warmup 3 > gpurun_out/r2_scale_n$n.json 2> gpurun_out/r2_scale_n$n.err
   tail -c 300 gpurun_out/r2_scale_n$n.err
 done
