@@ -78,7 +78,7 @@ def test_shard_packing_reads_the_c_structs_and_gathers_in_input_order():
 
 def test_whole_program_comparison_logic(tmp_path, monkeypatch):
     """bench.py's whole_program key with the reference binary standing in for the GPU program (no GPU here): identical VCFs
-    are reported as such; a perturbed record makes it rerun the reference and report that no reference run has that line."""
+    are reported as such, multi-threaded and in the strict single-threaded comparison; a perturbed record is reported by both."""
     import os
     import pytest
     import bench_configs as bc
@@ -95,9 +95,9 @@ def test_whole_program_comparison_logic(tmp_path, monkeypatch):
     stand_in.chmod(0o755)
     monkeypatch.setattr(bc, "ROOT", str(root))
     r = bc.run_whole_program(2, 4, 0)
-    assert r["vcf_identical"] and r["determinism"]["reference_runs"] == 1 and r["pass_records"] == 2 and r["records"] == 7
+    assert r["vcf_identical"] and r["determinism"]["records_differing_multi_threaded"] == [] and r["pass_records"] == 2 and r["records"] == 7
+    assert r["strict_single_thread"]["vcf_identical"] and r["strict_single_thread"]["records"] == 7
     monkeypatch.setenv("PERTURB", "1")
     r = bc.run_whole_program(2, 4, 0)
-    d = r["determinism"]
-    assert not r["vcf_identical"] and d["reference_runs"] == 3 and d["records_differing_from_first_reference_run"] == 1
-    assert not d["vcf_identical_to_a_reference_run"] and not d["every_differing_record_has_a_reference_run_with_the_same_line"]
+    assert not r["vcf_identical"] and len(r["determinism"]["records_differing_multi_threaded"]) == 1
+    assert not r["strict_single_thread"]["vcf_identical"]
