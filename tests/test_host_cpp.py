@@ -66,3 +66,18 @@ def test_gpu_programs_route_the_hot_path_to_the_library():
     if os.path.exists(ref):
         rs = subprocess.check_output(["nm", "-C", ref], text=True)
         assert "onvex" in rs and "polish_to_perfection" in rs          # the reference does instantiate both
+
+
+def test_pipeline_fibers_with_a_simulated_device(tmp_path):
+    """host/pipeline.hpp + fiber.hpp on the CPU (tests/cpp/pipeline_test.cpp): a collector thread stands in for the device.
+    A body (the reference's polish_variant in the real program) always continues on the thread that started it, a thread
+    never runs two bodies at once (per-thread BAM handles, sviper.h:133-135), parked bodies per thread stay under the cap,
+    bodies that never reach the device and a throwing body are handled, the idle hook fires."""
+    exe = str(tmp_path / "pipeline_test")
+    lib = os.path.join(ROOT, "sviper_b200", "csrc")
+    subprocess.check_call(["g++", "-std=c++14", "-O2", "-Wall", "-pedantic", "-Werror", "-fopenmp", "-I", ROOT,
+                           os.path.join(ROOT, "tests", "cpp", "pipeline_test.cpp"), "-o", exe, "-L", lib, "-lsviper_b200",
+                           "-Wl,-rpath," + lib, "-lpthread"])
+    for args in (("4", "2000", "8"), ("1", "300", "64"), ("8", "10000", "16")):
+        out = subprocess.check_output([exe] + list(args), text=True, timeout=300)
+        assert out.strip().endswith("ok"), out
