@@ -238,6 +238,7 @@ def run_sharded_c3(ctx, rank, world, flush, gloo, n_total, shard, t_gen, barrier
     rank 0 -- and, separately, HBM-resident (device events, max over ranks)."""
     import torch
     import torch.distributed as dist
+    from sviper_b200 import shard as shardlib
     owners = shard_records(n_total, world)
     assert len(owners[rank]) == len(shard)
     ctx.set_lanes(4)
@@ -254,16 +255,10 @@ def run_sharded_c3(ctx, rank, world, flush, gloo, n_total, shard, t_gen, barrier
         ctx.run_prepared(pb)
         t_dev = time.perf_counter() - t0
         if world > 1:
-            # host gather to rank 0 (gloo): sizes first, then the byte arrays as padded uint8 tensors
-            mine = torch.from_numpy(pack_shard(pb))
-            sizes = [torch.zeros(1, dtype=torch.int64) for _ in range(world)]
-            dist.all_gather(sizes, torch.tensor([mine.numel()], dtype=torch.int64), group=gloo)
-            cap = int(max(int(x) for x in sizes))
-            padded = torch.zeros(cap, dtype=torch.uint8); padded[:mine.numel()] = mine
-            bufs = [torch.zeros(cap, dtype=torch.uint8) for _ in range(world)] if rank == 0 else None
-            dist.gather(padded, bufs, dst=0, group=gloo)
+            # host gather to rank 0: payload through shared memory, sizes / completion through gloo (shard.gather_bytes)
+            parts = shardlib.gather_bytes(pack_shard(pb), rank, world, group=gloo)
             if rank == 0:
-                gathered = GatheredResults(n_total, owners, [b[:int(n)].numpy() for b, n in zip(bufs, sizes)])      # input order
+                gathered = GatheredResults(n_total, owners, parts)      # input order
         else:
             gathered = LocalResults(pb)       # one rank: the caller's result buffers ARE the input-ordered vector
         times.append((time.perf_counter() - t0, t_dev))
@@ -292,8 +287,8 @@ def run_sharded_c3(ctx, rank, world, flush, gloo, n_total, shard, t_gen, barrier
             "scaling": "strong", "variants": n_total, "n_gpus": world,
             "e2e_variants_per_s": n_total / e2e_s, "e2e_seconds": e2e_s,
             "e2e_includes": "staging + H2D + all kernels + D2H per rank; N > 1: packing the shard's results into one byte array, "
-                            "gloo gather to rank 0, input-order index over the gathered arrays (N = 1: the call's result buffers "
-                            "are already the input-ordered vector)",
+                            "host gather to rank 0 (payload through /dev/shm, sizes and completion through gloo), input-order "
+                            "index over the gathered arrays (N = 1: the call's result buffers are already the input-ordered vector)",
             "gather_seconds_rank0": times[-1][0] - times[-1][1],
             "resident_variants_per_s": n_total / (max(all_ms) * 1e-3), "resident_ms_per_rank": all_ms,
             "rank_imbalance_max_over_mean": max(all_ms) / (sum(all_ms) / len(all_ms)),
